@@ -1,0 +1,163 @@
+/*
+ * mused_b200 -- C ABI of the B200-native SWFD sketch-and-assign hot path.
+ *
+ * The reference (kelaendi/mused) is pure Python and has no FFI of its own; the
+ * drop-in boundary is the Python surface that main.py calls.  Each entry point
+ * below names the reference interface it stands behind (paths relative to the
+ * reference tree).  INTEGRATION.md shows the ctypes binding a maintainer adds.
+ *
+ * Conventions: extern "C", plain pointers and sizes, no torch / CUDA types in
+ * signatures (`stream` is a cudaStream_t passed as void*, NULL = default
+ * stream).  Every function returns 0 on success and a negative code on error;
+ * mused_last_error() returns the message of the calling thread's last error.
+ * A handle is bound to one device and is not thread-safe; distinct handles are
+ * independent.  There is no CPU fallback: without a CUDA device every call
+ * fails with MUSED_ERR_CUDA.
+ */
+#ifndef MUSED_B200_H
+#define MUSED_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MUSED_OK 0
+#define MUSED_ERR_ARG (-1)
+#define MUSED_ERR_CUDA (-2)
+#define MUSED_ERR_STATE (-3)
+#define MUSED_ERR_NOMEM (-4)
+
+/* element types accepted for incoming rows */
+#define MUSED_F64 0
+#define MUSED_F32 1
+#define MUSED_I64 2
+#define MUSED_I32 3
+#define MUSED_U8 4
+
+/* where a buffer lives */
+#define MUSED_HOST 0
+#define MUSED_DEVICE 1
+
+const char* mused_last_error(void);
+int mused_version(void);
+/* number of CUDA devices visible, or a negative error code */
+int mused_device_count(void);
+
+/* ---------------------------------------------------------------------------
+ * Sequence-based multi-level sliding-window Frequent Directions.
+ * Replaces swfd/seq_based_swfd.py:11-103 (SeqBasedSWFD) together with the
+ * per-level machinery of swfd/sliding_windows_frequent_directions.py:27-197
+ * (SlidingWindowFD) and swfd/frequent_directions.py:96-153
+ * (FrequentDirectionsWithDump).  Arithmetic is float64 like the reference.
+ * ------------------------------------------------------------------------- */
+typedef struct mused_swfd mused_swfd_t;
+
+typedef struct {
+    int64_t N;                /* window length            (seq_based_swfd.py:22)        */
+    int64_t d;                /* row dimension            (:23)                         */
+    int64_t ell;              /* sketch_dim               (:27)                         */
+    double beta;              /* queue cap (2+8/beta)*ell (:61)                         */
+    int32_t n_levels;         /* logR                     (:25 / :32)                   */
+    const double* thresholds; /* n_levels dump thresholds (:36 / :42), host pointer     */
+    int32_t device;           /* CUDA ordinal                                            */
+    int32_t cluster;          /* CTAs cooperating on one FD instance: 1,2,4,8; 0 = auto */
+    int64_t chunk_rows;       /* rows staged per launch; 0 = auto                        */
+} mused_swfd_cfg;
+
+int mused_swfd_create(mused_swfd_t** out, const mused_swfd_cfg* cfg);
+int mused_swfd_destroy(mused_swfd_t* h);
+
+/* SeqBasedSWFD.fit (seq_based_swfd.py:47-80) applied to n_rows consecutive rows
+ * in arrival order; n_rows = 1 is exactly one reference call.  `rows` is
+ * row-major with leading dimension `ld` elements of `dtype`, on the host or on
+ * the handle's device.  The rows are copied; the caller may reuse the buffer
+ * when the call returns (host) / when `stream` reaches this point (device). */
+int mused_swfd_fit(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld,
+                   int dtype, int where, void* stream);
+
+/* SeqBasedSWFD.get (seq_based_swfd.py:83-100 -> sliding_windows_...py:154-173).
+ * Like the reference it flushes the chosen level's pending rows (a state
+ * mutation).  sketch: ell x d, sigma2: ell, vt: ell x d (may be NULL),
+ * delta: 1, level: chosen level j.  Output buffers live on `where`. */
+int mused_swfd_get(mused_swfd_t* h, double* sketch, double* sigma2, double* vt,
+                   double* delta, int32_t* level, int where, void* stream);
+
+/* SeqBasedSWFD.get_size (seq_based_swfd.py:102-103). */
+int mused_swfd_size(mused_swfd_t* h, int64_t* n);
+
+/* Rows consumed so far (SeqBasedSWFD.time). */
+int mused_swfd_time(mused_swfd_t* h, uint64_t* t);
+
+/* Introspection for the differential tests: per FD instance (2 per level,
+ * index 2*level + side, side 0 = the reference's current `fd`, 1 = `fd_aux`)
+ * energy, delta, pending rows, last_dump_time, queue length, flush/dump counts.
+ * scal: n_inst x 8 doubles {energy, delta, pending, last_dump_time, q_len,
+ * n_flush, n_dump, n_raw}; sigma2: n_inst x ell; q_s/q_t: n_inst x q_cap
+ * (first q_len valid, oldest first).  Host buffers; any may be NULL. */
+int mused_swfd_debug(mused_swfd_t* h, double* scal, double* sigma2, uint64_t* q_s,
+                     uint64_t* q_t, int64_t q_cap);
+int mused_swfd_queue_capacity(mused_swfd_t* h, int64_t* q_cap);
+
+/* ---------------------------------------------------------------------------
+ * One Frequent Directions instance with row buffer and dump.
+ * Replaces swfd/frequent_directions.py:96-153 (FrequentDirectionsWithDump) and,
+ * with error = +inf and explicit batches, :79-93 (RobustFrequentDirections).
+ * ------------------------------------------------------------------------- */
+typedef struct mused_fd mused_fd_t;
+
+int mused_fd_create(mused_fd_t** out, int64_t d, int64_t ell, double error, int device,
+                    int cluster);
+int mused_fd_destroy(mused_fd_t* h);
+/* FrequentDirectionsWithDump.fit row by row (:115-125); no dump is taken. */
+int mused_fd_fit(mused_fd_t* h, const void* rows, int64_t n_rows, int64_t ld, int dtype,
+                 int where, void* stream);
+/* FrequentDirections.fit(X, batch_size) (:39-58): shrink after every
+ * batch_size rows (and after the ragged tail), no energy rule. */
+int mused_fd_fit_batches(mused_fd_t* h, const void* rows, int64_t n_rows, int64_t ld,
+                         int dtype, int where, int64_t batch_size, void* stream);
+/* FrequentDirectionsWithDump.dump (:127-142): *dumped = 1 and v (d doubles on
+ * `where`) filled when sigma2[0] >= error, else *dumped = 0. */
+int mused_fd_dump(mused_fd_t* h, double* v, int32_t* dumped, int where, void* stream);
+int mused_fd_flush(mused_fd_t* h, void* stream);
+/* get (:144-146): flushes, then returns (sketch, sigma2, vt, delta). */
+int mused_fd_get(mused_fd_t* h, double* sketch, double* sigma2, double* vt, double* delta,
+                 int where, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * Similarity / assignment operators of matrix_operations.py.
+ * ------------------------------------------------------------------------- */
+#define MUSED_METRIC_COSINE 0 /* matrix_operations.py:106 cosine_similarity          */
+#define MUSED_METRIC_L2 1     /* :118 NearestNeighbors (Euclidean), :286-289 argmin  */
+
+/* Fused cosine-similarity + threshold + argmax event assignment (north_star
+ * operator; nearest reference code matrix_operations.py:106 and :286-289).
+ * X: n x d float32 rows (ld_x), C: k x d float32 centroids (ld_c), all device.
+ * metric COSINE: label = argmax_j cos(x, c_j) if that cosine >= tau else -1;
+ * metric L2:     label = argmin_j ||x - c_j||  if that distance <= tau else -1
+ *                (tau < 0 disables the threshold).  Ties -> lowest j.
+ * score (nullable): best cosine / best distance. */
+int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float* C,
+                 int64_t k, int64_t ld_c, int metric, float tau, int32_t* labels,
+                 float* score, void* stream);
+
+/* kNN adjacency of one dense modality, OR-accumulated into a fused uint8
+ * W x W matrix (create_adjacency_matrix numeric branches
+ * matrix_operations.py:101-108 cosine top-k, :112-119 Euclidean kNN, writer
+ * :123-130, and fuse_matrices :134-141).  feats: W x f float32 device; every
+ * row i sets adj[i, j] = 1 for its k best j (self excluded after selection
+ * exactly like the reference: the top-k list may contain i itself). */
+int mused_topk_adjacency(const float* feats, int64_t W, int64_t f, int64_t ld, int metric,
+                         int64_t k, uint8_t* adj, void* stream);
+
+/* Contingency table for match_clusters (matrix_operations.py:169-172):
+ * counts[p * Q + q] = #{i : prev[i] == p and cur[i] == q}; labels outside
+ * [0,P) x [0,Q) are ignored.  Device pointers. */
+int mused_contingency(const int32_t* prev, const int32_t* cur, int64_t n, int32_t P,
+                      int32_t Q, int32_t* counts, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MUSED_B200_H */

@@ -1,0 +1,289 @@
+// Similarity / assignment operators of matrix_operations.py as sm_100a kernels.
+//   mused_assign          fused cosine|L2 + threshold + argmax|argmin (north_star operator;
+//                         nearest reference code matrix_operations.py:106, :286-289)
+//   mused_topk_adjacency  kNN -> 0/1 adjacency, OR-fused (matrix_operations.py:101-141)
+//   mused_contingency     overlap counts of match_clusters (matrix_operations.py:169-172)
+#include <float.h>
+#include "common.cuh"
+
+namespace mused {
+
+constexpr int AT = 64;   // rows / centroids per tile
+constexpr int AK = 32;   // k chunk (floats)
+
+struct AssignSmem {
+    float a[AK][AT + 4];
+    float b[AK][AT + 4];
+};
+
+// squared row norms of a small matrix (centroids / features)
+__global__ void k_row_norm2_f32(const float* __restrict__ X, long long n, long long d, long long ld,
+                                float* __restrict__ out) {
+    const long long r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (r >= n) return;
+    const float* x = X + (size_t)r * ld;
+    float acc = 0.f;
+    for (long long c = threadIdx.x & 31; c < d; c += 32) acc = fmaf(x[c], x[c], acc);
+    acc = warp_sum_f(acc);
+    if ((threadIdx.x & 31) == 0) out[r] = acc;
+}
+
+// 64 x 64 tile of X C^T in fp32 (16x16 threads, 4x4 micro-tile); the squared
+// norm of each X row falls out of the same pass (tx == 0 lanes accumulate it).
+__device__ __forceinline__ void dot_tile_f32(AssignSmem& sm, const float* __restrict__ X,
+                                             long long n, long long ldx, const float* __restrict__ C,
+                                             long long k, long long ldc, long long d, long long r0,
+                                             long long c0, float acc[4][4], float xn[4]) {
+    const int t = threadIdx.x, ty = t >> 4, tx = t & 15;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        xn[i] = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    }
+    for (long long k0 = 0; k0 < d; k0 += AK) {
+#pragma unroll
+        for (int e = t; e < AT * AK; e += 256) {
+            const int kk = e & (AK - 1), mm = e >> 5;
+            const long long r = r0 + mm, c = k0 + kk;
+            sm.a[kk][mm] = (r < n && c < d) ? X[(size_t)r * ldx + c] : 0.f;
+            const long long cr = c0 + mm;
+            sm.b[kk][mm] = (cr < k && c < d) ? C[(size_t)cr * ldc + c] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < AK; ++kk) {
+            float av[4], bv[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) av[i] = sm.a[kk][ty * 4 + i];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) bv[j] = sm.b[kk][tx * 4 + j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                xn[i] = fmaf(av[i], av[i], xn[i]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// One CTA per 64 rows of X; loops over centroid tiles keeping the running best.
+__global__ void __launch_bounds__(256) k_assign(const float* __restrict__ X, long long n, long long d,
+                                                long long ldx, const float* __restrict__ C, long long k,
+                                                long long ldc, const float* __restrict__ cn2, int metric,
+                                                float tau, int* __restrict__ labels,
+                                                float* __restrict__ score) {
+    __shared__ AssignSmem sm;
+    const int t = threadIdx.x, ty = t >> 4, tx = t & 15;
+    for (long long r0 = (long long)blockIdx.x * AT; r0 < n; r0 += (long long)gridDim.x * AT) {
+        float best[4];
+        int bidx[4];
+        float xn_keep[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { best[i] = -FLT_MAX; bidx[i] = 0x7fffffff; }
+        for (long long c0 = 0; c0 < k; c0 += AT) {
+            float acc[4][4], xn[4];
+            dot_tile_f32(sm, X, n, ldx, C, k, ldc, d, r0, c0, acc, xn);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                xn_keep[i] = xn[i];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const long long cj = c0 + tx * 4 + j;
+                    if (cj >= k) continue;
+                    const float c2 = cn2[cj];
+                    float key;  // larger is better for both metrics
+                    if (metric == MUSED_METRIC_COSINE) {
+                        // sklearn normalises with norm 0 -> 1 (cosine of a zero row is 0)
+                        key = acc[i][j] * rsqrtf(c2 > 0.f ? c2 : 1.f);
+                    } else {
+                        key = -(c2 - 2.f * acc[i][j]);  // -(||c||^2 - 2 x.c); ||x||^2 is common
+                    }
+                    if (key > best[i] || (key == best[i] && (int)cj < bidx[i])) {
+                        best[i] = key;
+                        bidx[i] = (int)cj;
+                    }
+                }
+            }
+        }
+        // reduce over the 16 tx lanes that share a row (same half-warp)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) {
+                const float ob = __shfl_xor_sync(0xffffffffu, best[i], o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bidx[i], o);
+                if (ob > best[i] || (ob == best[i] && oi < bidx[i])) { best[i] = ob; bidx[i] = oi; }
+            }
+            const long long r = r0 + ty * 4 + i;
+            if (tx == 0 && r < n) {
+                const float x2 = xn_keep[i];
+                float sc;
+                bool keep;
+                if (metric == MUSED_METRIC_COSINE) {
+                    sc = best[i] * rsqrtf(x2 > 0.f ? x2 : 1.f);
+                    keep = sc >= tau;
+                } else {
+                    sc = sqrtf(fmaxf(x2 - best[i], 0.f));
+                    keep = (tau < 0.f) || (sc <= tau);
+                }
+                labels[r] = keep ? bidx[i] : -1;
+                if (score) score[r] = sc;
+            }
+        }
+    }
+}
+
+// S = similarity key matrix (W x W, larger = closer) for the adjacency operator.
+__global__ void __launch_bounds__(256) k_pair_keys(const float* __restrict__ F, long long W, long long f,
+                                                   long long ld, const float* __restrict__ n2, int metric,
+                                                   float* __restrict__ S) {
+    __shared__ AssignSmem sm;
+    const int t = threadIdx.x, ty = t >> 4, tx = t & 15;
+    const long long tiles = (W + AT - 1) / AT;
+    for (long long tile = blockIdx.x; tile < tiles * tiles; tile += gridDim.x) {
+        const long long r0 = (tile / tiles) * AT, c0 = (tile % tiles) * AT;
+        float acc[4][4], xn[4];
+        dot_tile_f32(sm, F, W, ld, F, W, ld, f, r0, c0, acc, xn);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const long long r = r0 + ty * 4 + i;
+            if (r >= W) continue;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const long long c = c0 + tx * 4 + j;
+                if (c >= W) continue;
+                float key;
+                if (metric == MUSED_METRIC_COSINE) {
+                    const float a2 = n2[r], b2 = n2[c];
+                    key = acc[i][j] * rsqrtf(a2 > 0.f ? a2 : 1.f) * rsqrtf(b2 > 0.f ? b2 : 1.f);
+                } else {
+                    key = (r == c) ? 0.f : -fmaxf(n2[r] + n2[c] - 2.f * acc[i][j], 0.f);
+                }
+                S[(size_t)r * W + c] = key;
+            }
+        }
+    }
+}
+
+// per row: k best keys (ties -> lowest index), adj[i][j] |= 1 for j != i.
+__global__ void __launch_bounds__(256) k_topk_rows(const float* __restrict__ S, long long W, long long k,
+                                                   unsigned char* __restrict__ adj) {
+    extern __shared__ float row[];
+    __shared__ float rb[8];
+    __shared__ int ri[8];
+    for (long long i = blockIdx.x; i < W; i += gridDim.x) {
+        for (long long c = threadIdx.x; c < W; c += 256) row[c] = S[(size_t)i * W + c];
+        __syncthreads();
+        const long long kk = k < W ? k : W;
+        for (long long it = 0; it < kk; ++it) {
+            float b = -FLT_MAX;
+            int bi = 0x7fffffff;
+            for (long long c = threadIdx.x; c < W; c += 256) {
+                const float v = row[c];
+                if (v > b) { b = v; bi = (int)c; }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ob = __shfl_xor_sync(0xffffffffu, b, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (ob > b || (ob == b && oi < bi)) { b = ob; bi = oi; }
+            }
+            if ((threadIdx.x & 31) == 0) { rb[threadIdx.x >> 5] = b; ri[threadIdx.x >> 5] = bi; }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                for (int q = 1; q < 8; ++q)
+                    if (rb[q] > b || (rb[q] == b && ri[q] < bi)) { b = rb[q]; bi = ri[q]; }
+                if (bi != 0x7fffffff) {
+                    row[bi] = -FLT_MAX;  // taken (an all -FLT_MAX row simply stops matching)
+                    if (bi != (int)i) adj[(size_t)i * W + bi] = 1;
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+__global__ void k_contingency(const int* __restrict__ prev, const int* __restrict__ cur, long long n, int P,
+                              int Q, int* __restrict__ counts) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int p = prev[i], q = cur[i];
+        if (p >= 0 && p < P && q >= 0 && q < Q) atomicAdd(&counts[(size_t)p * Q + q], 1);
+    }
+}
+
+static int sm_count_of_current() {
+    int dev = 0, n = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    return n;
+}
+
+}  // namespace mused
+
+using namespace mused;
+
+extern "C" {
+
+int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float* C, int64_t k,
+                 int64_t ld_c, int metric, float tau, int32_t* labels, float* score, void* stream) {
+    MUSED_REQUIRE(n >= 0 && d >= 1 && k >= 1 && ld_x >= d && ld_c >= d, "bad shape");
+    MUSED_REQUIRE(X && C && labels, "NULL argument");
+    MUSED_REQUIRE(metric == MUSED_METRIC_COSINE || metric == MUSED_METRIC_L2, "unknown metric %d", metric);
+    if (n == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    float* cn2 = nullptr;
+    MUSED_CUDA(cudaMallocAsync((void**)&cn2, sizeof(float) * (size_t)k, st));
+    k_row_norm2_f32<<<(unsigned)((k + 7) / 8), 256, 0, st>>>(C, k, d, ld_c, cn2);
+    MUSED_CUDA(cudaGetLastError());
+    const long long tiles = (n + AT - 1) / AT;
+    const int grid = (int)std::min<long long>(tiles, 16ll * sm_count_of_current());
+    k_assign<<<grid, 256, 0, st>>>(X, n, d, ld_x, C, k, ld_c, cn2, metric, tau, labels, score);
+    MUSED_CUDA(cudaGetLastError());
+    MUSED_CUDA(cudaFreeAsync(cn2, st));
+    return 0;
+}
+
+int mused_topk_adjacency(const float* feats, int64_t W, int64_t f, int64_t ld, int metric, int64_t k,
+                         uint8_t* adj, void* stream) {
+    MUSED_REQUIRE(W >= 1 && f >= 1 && ld >= f && k >= 0, "bad shape");
+    MUSED_REQUIRE(feats && adj, "NULL argument");
+    MUSED_REQUIRE(metric == MUSED_METRIC_COSINE || metric == MUSED_METRIC_L2, "unknown metric %d", metric);
+    MUSED_REQUIRE(W * 4 <= 200 * 1024, "window of %lld rows exceeds the per-row shared-memory select (max 51200)", (long long)W);
+    if (k == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    float *n2 = nullptr, *S = nullptr;
+    MUSED_CUDA(cudaMallocAsync((void**)&n2, sizeof(float) * (size_t)W, st));
+    MUSED_CUDA(cudaMallocAsync((void**)&S, sizeof(float) * (size_t)W * W, st));
+    k_row_norm2_f32<<<(unsigned)((W + 7) / 8), 256, 0, st>>>(feats, W, f, ld, n2);
+    MUSED_CUDA(cudaGetLastError());
+    const long long tiles = ((W + AT - 1) / AT) * ((W + AT - 1) / AT);
+    const int sms = sm_count_of_current();
+    k_pair_keys<<<(int)std::min<long long>(tiles, 16ll * sms), 256, 0, st>>>(feats, W, f, ld, n2, metric, S);
+    MUSED_CUDA(cudaGetLastError());
+    const size_t smem = (size_t)W * sizeof(float);
+    MUSED_CUDA(cudaFuncSetAttribute(k_topk_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_topk_rows<<<(int)std::min<long long>(W, 8ll * sms), 256, smem, st>>>(S, W, k, adj);
+    MUSED_CUDA(cudaGetLastError());
+    MUSED_CUDA(cudaFreeAsync(S, st));
+    MUSED_CUDA(cudaFreeAsync(n2, st));
+    return 0;
+}
+
+int mused_contingency(const int32_t* prev, const int32_t* cur, int64_t n, int32_t P, int32_t Q,
+                      int32_t* counts, void* stream) {
+    MUSED_REQUIRE(n >= 0 && P >= 1 && Q >= 1, "bad shape");
+    MUSED_REQUIRE((prev && cur) || n == 0, "NULL argument");
+    MUSED_REQUIRE(counts, "NULL argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    MUSED_CUDA(cudaMemsetAsync(counts, 0, sizeof(int32_t) * (size_t)P * Q, st));
+    if (n == 0) return 0;
+    const int grid = (int)std::min<long long>((n + 255) / 256, 4ll * sm_count_of_current());
+    k_contingency<<<grid, 256, 0, st>>>(prev, cur, n, P, Q, counts);
+    MUSED_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,136 @@
+"""Numeric operators of /root/reference/matrix_operations.py on the B200.
+
+Same names and argument meaning as the reference for the functions main.py
+imports on the SWFDMC path; string modalities (username / tags / TF-IDF
+vocabulary building, matrix_operations.py:55-100) are host-side string
+processing and out of scope -- this module takes
+the dense feature matrices those branches produce.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib
+
+_METRIC = {"cosine": _lib.METRIC_COSINE, "text": _lib.METRIC_COSINE,
+           "euclidean": _lib.METRIC_L2, "l2": _lib.METRIC_L2}
+
+
+def _dev_f32(x, device):
+    if isinstance(x, torch.Tensor):
+        return x.to(device=device, dtype=torch.float32).contiguous()
+    return torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(device)
+
+
+def cosine_assign(X, centroids, threshold, *, metric="cosine", device="cuda:0", return_score=False):
+    """Fused similarity + threshold + argmax event assignment (north_star operator).
+
+    label[i] = argmax_j cos(X[i], centroids[j]) if that cosine >= threshold else -1
+    (metric="l2": argmin distance, kept when distance <= threshold, threshold < 0 = always).
+    Nearest reference code: matrix_operations.py:106 (cosine_similarity) and :286-289 (argmin).
+    Returns int32 labels (torch tensor on ``device``) [and float32 scores].
+    """
+    lib = _lib.load()
+    Xd, Cd = _dev_f32(X, device), _dev_f32(centroids, device)
+    if Xd.dim() != 2 or Cd.dim() != 2 or Xd.shape[1] != Cd.shape[1]:
+        raise ValueError("X (n x d) and centroids (k x d) must share d")
+    n, d = Xd.shape
+    labels = torch.empty(n, dtype=torch.int32, device=Xd.device)
+    score = torch.empty(n, dtype=torch.float32, device=Xd.device)
+    with torch.cuda.device(Xd.device):
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(lib.mused_assign(Xd.data_ptr(), n, d, Xd.stride(0) if n > 1 else d, Cd.data_ptr(),
+                                    Cd.shape[0], Cd.stride(0) if Cd.shape[0] > 1 else d,
+                                    _METRIC[metric], float(threshold), labels.data_ptr(),
+                                    score.data_ptr(), st))
+    return (labels, score) if return_score else labels
+
+
+def topk_adjacency(features, k, *, metric="cosine", out=None, device="cuda:0"):
+    """kNN adjacency of one dense modality, OR-accumulated into ``out`` (uint8 W x W).
+
+    cosine: matrix_operations.py:101-108 (k = k_basis + 1 there); euclidean:
+    :112-119 (k = k_basis); writer :123-130 (directed, no self edges).
+    """
+    lib = _lib.load()
+    F = _dev_f32(features, device)
+    W, f = F.shape
+    if out is None:
+        out = torch.zeros((W, W), dtype=torch.uint8, device=F.device)
+    with torch.cuda.device(F.device):
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(lib.mused_topk_adjacency(F.data_ptr(), W, f, F.stride(0) if W > 1 else f,
+                                            _METRIC[metric], int(k), out.data_ptr(), st))
+    return out
+
+
+def create_adjacency_matrix(data, modality_type, k_basis=50, *, device="cuda:0"):
+    """Dense numeric branches of matrix_operations.py:14-132 -> W x W float64 0/1 ndarray.
+
+    modality_type "text"/"cosine": rows are (TF-IDF or embedding) vectors, cosine top-(k_basis+1);
+    anything else: Euclidean kNN with k = k_basis (the reference's default branch).
+    """
+    A = np.asarray(data, dtype=np.float64)
+    W = A.shape[0]
+    out = np.zeros((W, W))
+    valid = np.where(np.all(np.isfinite(A), axis=1))[0]           # :114
+    if len(valid) == 0:
+        return out
+    if modality_type in ("text", "cosine"):
+        k, metric = k_basis + 1, "cosine"                          # :101
+    else:
+        k, metric = max(1, k_basis), "euclidean"                   # :112, :118
+    adj = topk_adjacency(A[valid], min(k, len(valid)), metric=metric, device=device).cpu().numpy()
+    out[np.ix_(valid, valid)] = adj
+    return out
+
+
+def fuse_matrices(matrices):
+    """Element-wise OR of adjacency matrices -> int64 (matrix_operations.py:134-141)."""
+    dev = None
+    acc = None
+    for m in matrices:
+        t = m if isinstance(m, torch.Tensor) else torch.as_tensor(np.asarray(m))
+        t = t.to("cuda:0") if not t.is_cuda else t
+        dev = dev or t.device
+        b = t != 0
+        acc = b if acc is None else (acc | b)
+    out = acc.to(torch.int64)
+    if isinstance(matrices[0], torch.Tensor):
+        return out
+    return out.cpu().numpy().astype(int)
+
+
+def contingency(prev_clusters, new_clusters, P, Q, *, device="cuda:0"):
+    """counts[p, q] = #{i: prev[i] == p and new[i] == q} (matrix_operations.py:169-172)."""
+    lib = _lib.load()
+    p = torch.as_tensor(np.asarray(prev_clusters), dtype=torch.int32).to(device)
+    q = torch.as_tensor(np.asarray(new_clusters), dtype=torch.int32).to(device)
+    counts = torch.empty((P, Q), dtype=torch.int32, device=p.device)
+    with torch.cuda.device(p.device):
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(lib.mused_contingency(p.data_ptr(), q.data_ptr(), p.numel(), P, Q, counts.data_ptr(), st))
+    return counts
+
+
+def match_clusters(prev_clusters, new_clusters, method="hungarian", min_overlap=5, *, device="cuda:0"):
+    """matrix_operations.py:155-185 + :212-233: overlap counts on the GPU (one
+    histogram pass instead of the O(P*Q*W) loop), Hungarian on the host."""
+    from scipy.optimize import linear_sum_assignment
+    if prev_clusters is None or len(prev_clusters) == 0:
+        return new_clusters
+    prev_clusters = np.asarray(prev_clusters)
+    new_clusters = np.asarray(new_clusters)
+    unique_prev, ip = np.unique(prev_clusters, return_inverse=True)
+    unique_new, iq = np.unique(new_clusters, return_inverse=True)
+    counts = contingency(ip, iq, len(unique_prev), len(unique_new), device=device).cpu().numpy()
+    cost = np.where(counts >= min_overlap, -counts.astype(float), np.inf)
+    if (np.all(np.isinf(cost)) or np.any(np.all(np.isinf(cost), axis=1))
+            or np.any(np.all(np.isinf(cost), axis=0))):           # is_feasible :226-233
+        return new_clusters
+    if method != "hungarian":
+        raise ValueError("Invalid method. Choose 'hungarian' or 'pot'.")  # 'pot' needs POT (absent)
+    row_ind, col_ind = linear_sum_assignment(cost)
+    mapping = {unique_new[c]: unique_prev[r] for r, c in zip(row_ind, col_ind)}
+    return np.array([mapping.get(c, c) for c in new_clusters])

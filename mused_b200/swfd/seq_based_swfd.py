@@ -1,0 +1,121 @@
+"""SeqBasedSWFD on the B200 engine -- same constructor, ``fit``, ``get`` and
+``get_size`` as /root/reference/swfd/seq_based_swfd.py:11-103.
+
+Host code only sizes the level ladder (``logR``, thresholds) exactly like the
+reference constructor and forwards rows; every per-row decision and all
+arithmetic run in the CUDA engine (csrc/swfd_device.cuh) through the C ABI.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from .. import _lib
+
+
+class SeqBasedSWFD:
+    def __init__(self, N: int, R: float, d: int, sketch_dim: int, beta: float = 1.0, *,
+                 device: int = 0, cluster: int = 0, chunk_rows: int = 0, **kwargs):
+        """Sliding Window on Frequent Directions (seq_based_swfd.py:12-44).
+
+        Args (reference): N window size, R upper bound of squared row norm,
+        d row dimension, sketch_dim, beta; kwarg ``upper_F_norm`` switches the
+        level count to ceil(log2(F/N)) (:31-37).
+        Extras (keyword-only): device ordinal, cluster (CTAs per FD instance,
+        0 = auto), chunk_rows (rows staged per launch).
+        """
+        self.N = np.uint64(N)
+        self.d = int(d)
+        self.R = R
+        self.logR = int(np.ceil(np.log2(R)))                       # :25
+        self.beta = beta
+        self.sketch_dim = int(sketch_dim)
+        if "upper_F_norm" in kwargs:                               # :31-37
+            self.logR = int(np.ceil(np.log2(kwargs["upper_F_norm"] / self.N)))
+            base = self.N / self.sketch_dim
+            thr = [float(base * (2 ** j)) for j in range(self.logR)]
+        else:                                                      # :39-42
+            thr = [float((2 ** j) * self.N / self.sketch_dim) for j in range(self.logR)]
+        self.logR = max(self.logR, 0) if self.logR < 0 else self.logR
+        self.thresholds = thr
+        lib = _lib.load()
+        arr = (C.c_double * max(1, len(thr)))(*thr)
+        cfg = _lib.SwfdCfg(int(N), self.d, self.sketch_dim, float(beta), len(thr), arr,
+                           int(device), int(cluster), int(chunk_rows))
+        self._h = C.c_void_p()
+        _lib.check(lib.mused_swfd_create(C.byref(self._h), C.byref(cfg)))
+        self._lib = lib
+
+    # -- reference API -----------------------------------------------------
+    def fit(self, X):
+        """Handle the arriving row(s) (seq_based_swfd.py:47-80).
+
+        X: (1, d) like the reference, or (n, d) = n consecutive arrivals in
+        order (identical to n single calls).  numpy (host) or torch (host or
+        CUDA) float64 / float32 / int64 / int32 / uint8 rows; copied.
+        """
+        keep, ptr, n, ld, dt, where = _lib.rows_arg(X, self.d)
+        _lib.check(self._lib.mused_swfd_fit(self._h, ptr, n, ld, dt, where, None))
+        del keep
+
+    def get(self):
+        """(sketch l x d, sigma_squared l, Vt l x d, delta) -- seq_based_swfd.py:83-100."""
+        ell, d = self.sketch_dim, self.d
+        sketch = np.empty((ell, d))
+        s2 = np.empty(ell)
+        vt = np.empty((ell, d))
+        delta = C.c_double(0.0)
+        level = C.c_int32(0)
+        if self.logR <= 0:
+            raise KeyError(0)                                      # what the reference does
+        _lib.check(self._lib.mused_swfd_get(self._h, sketch.ctypes.data, s2.ctypes.data,
+                                            vt.ctypes.data, C.byref(delta), C.byref(level),
+                                            _lib.HOST, None))
+        self.last_level = int(level.value)
+        return sketch, s2, vt, float(delta.value)
+
+    def get_size(self):
+        n = C.c_int64(0)
+        _lib.check(self._lib.mused_swfd_size(self._h, C.byref(n)))
+        return int(n.value)
+
+    # -- extras --------------------------------------------------------------
+    @property
+    def time(self):
+        t = C.c_uint64(0)
+        _lib.check(self._lib.mused_swfd_time(self._h, C.byref(t)))
+        return np.uint64(t.value)
+
+    def debug_state(self):
+        """Per FD instance state in the layout of oracle.swfd_oracle.SeqSWFD.debug_state."""
+        S = 2 * len(self.thresholds)
+        cap = C.c_int64(0)
+        _lib.check(self._lib.mused_swfd_queue_capacity(self._h, C.byref(cap)))
+        cap = int(cap.value)
+        scal = np.zeros((max(S, 1), 8))
+        s2 = np.zeros((max(S, 1), self.sketch_dim))
+        qs = np.zeros((max(S, 1), cap), dtype=np.uint64)
+        qt = np.zeros((max(S, 1), cap), dtype=np.uint64)
+        _lib.check(self._lib.mused_swfd_debug(self._h, scal.ctypes.data, s2.ctypes.data,
+                                              qs.ctypes.data, qt.ctypes.data, cap))
+        out = []
+        for o in range(S):
+            ql = int(scal[o, 4])
+            out.append(dict(level=o // 2, energy=float(scal[o, 0]), delta=float(scal[o, 1]),
+                            pending=int(scal[o, 2]), last_dump_time=int(scal[o, 3]),
+                            s2=s2[o].copy(), q_s=[int(v) for v in qs[o, :ql]],
+                            q_t=[int(v) for v in qt[o, :ql]], n_flush=int(scal[o, 5]),
+                            n_dump=int(scal[o, 6]), n_raw=int(scal[o, 7])))
+        return out
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.mused_swfd_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,80 @@
+"""NumPy (float64) restatements of the similarity / assignment operators.
+TEST INFRASTRUCTURE ONLY (see oracle/__init__.py).
+
+``cosine_assign`` is the north_star operator; the reference has no such
+function, so its parity is UNPINNED by any reference
+test -- the restatement follows sklearn's cosine_similarity semantics used at
+matrix_operations.py:106 (rows L2-normalised, zero rows keep norm 1) plus
+np.argmax, and the nearest-centroid rule of matrix_operations.py:286-289.
+``knn_adjacency`` follows matrix_operations.py:101-108 / :112-119 / :123-130 and
+is checked against the imported reference by tests/test_oracle_golden.py.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def _normalize(X):
+    n = np.linalg.norm(X, axis=1, keepdims=True)
+    n[n == 0] = 1.0
+    return X / n
+
+
+def cosine_assign(X, C, tau):
+    X = np.asarray(X, dtype=np.float64)
+    C = np.asarray(C, dtype=np.float64)
+    S = _normalize(X) @ _normalize(C).T
+    j = np.argmax(S, axis=1)
+    best = S[np.arange(len(X)), j]
+    labels = np.where(best >= tau, j, -1).astype(np.int32)
+    srt = np.sort(S, axis=1)
+    gap = srt[:, -1] - srt[:, -2] if S.shape[1] > 1 else np.full(len(X), np.inf)
+    return labels, best, gap
+
+
+def l2_assign(X, C, tau):
+    X = np.asarray(X, dtype=np.float64)
+    C = np.asarray(C, dtype=np.float64)
+    D = np.sqrt(np.maximum((X * X).sum(1)[:, None] + (C * C).sum(1)[None, :] - 2 * X @ C.T, 0))
+    j = np.argmin(D, axis=1)
+    best = D[np.arange(len(X)), j]
+    labels = np.where((tau < 0) | (best <= tau), j, -1).astype(np.int32)
+    srt = np.sort(D, axis=1)
+    gap = srt[:, 1] - srt[:, 0] if D.shape[1] > 1 else np.full(len(X), np.inf)
+    return labels, best, gap
+
+
+def knn_keys(F, metric):
+    F = np.asarray(F, dtype=np.float64)
+    if metric == "cosine":
+        Fn = _normalize(F)
+        return Fn @ Fn.T
+    sq = (F * F).sum(1)
+    K = -np.maximum(sq[:, None] + sq[None, :] - 2 * F @ F.T, 0)
+    np.fill_diagonal(K, 0.0)
+    return K
+
+
+def knn_adjacency(F, k, metric):
+    """Directed 0/1 adjacency; returns (adj, margin) where margin[i] is the key gap
+    between the k-th and (k+1)-th neighbour (near-tie detector)."""
+    K = knn_keys(F, metric)
+    W = K.shape[0]
+    k = min(k, W)
+    order = np.argsort(-K, axis=1, kind="stable")
+    adj = np.zeros((W, W), dtype=np.uint8)
+    for i in range(W):
+        for j in order[i, :k]:
+            if j != i:
+                adj[i, j] = 1
+    srt = -np.sort(-K, axis=1)
+    margin = srt[:, k - 1] - srt[:, k] if k < W else np.full(W, np.inf)
+    return adj, margin
+
+
+def contingency(prev, cur, P, Q):
+    out = np.zeros((P, Q), dtype=np.int32)
+    for p, q in zip(prev, cur):
+        if 0 <= p < P and 0 <= q < Q:
+            out[p, q] += 1
+    return out

@@ -1,0 +1,116 @@
+"""CPU: the oracle restatement against the committed reference outputs
+(tests/golden/*.npz, produced by oracle/gen_golden.py from the unmodified
+reference) and, when /root/reference is present, against the reference live."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import ref_shim, swfd_oracle as so, ops_oracle
+
+SEQ_CASES = ["seq_lowrank", "seq_heavytail", "seq_adjacency01", "seq_wide"]
+
+
+def _rows(A, t):
+    return A[t:t + 1] if A.dtype == np.int64 else A[t:t + 1].astype(np.float64)
+
+
+@pytest.mark.parametrize("name", SEQ_CASES)
+def test_oracle_matches_reference_outputs(golden_dir, name):
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    A, N, ell, qstep = g["A"], int(g["N"]), int(g["ell"]), int(g["qstep"])
+    sk = so.SeqSWFD(N, float(g["R"]), A.shape[1], ell)
+    assert sk.logR == int(g["n_levels"])
+    qi = 0
+    for t in range(A.shape[0]):
+        sk.fit(_rows(A, t))
+        if (t + 1) % qstep == 0:
+            assert sk.get_size() == int(g["size"][qi])
+            sketch, s2, vt, delta = sk.get()
+            # same LAPACK -> bit identical; another LAPACK build -> rounding-level
+            np.testing.assert_allclose(s2, g["sigma2"][qi], rtol=1e-9, atol=1e-9 * g["sigma2"][qi].max())
+            np.testing.assert_allclose(sketch.T @ sketch, g["gram"][qi], rtol=0, atol=1e-9 * np.abs(g["gram"][qi]).max())
+            assert delta == g["delta"][qi]
+            A64 = A.astype(np.float64)
+            err = so.cov_error(A64[max(0, t + 1 - N):t + 1], sketch)
+            assert abs(err - g["cov_err"][qi]) <= 1e-9 * g["cov_err"][qi]
+            assert err <= 4.0 / ell          # DS-FD bound used by swfd/test_bibd.py:80-81
+            qi += 1
+    st = sk.debug_state()
+    assert [o["last_dump_time"] for o in st] == list(g["fin_last_dump"])
+    assert [o["pending"] for o in st] == list(g["fin_pending"])
+    assert [len(o["q_s"]) for o in st] == list(g["fin_qlen"])
+    assert sum((o["q_s"] for o in st), []) == list(g["fin_qs"])
+    assert sum((o["q_t"] for o in st), []) == list(g["fin_qt"])
+
+
+def test_oracle_fd_dump_golden(golden_dir):
+    g = np.load(os.path.join(golden_dir, "fd_dump.npz"))
+    A = g["A"].astype(np.float64)
+    fd = so.FDDump(A.shape[1], int(g["ell"]), float(g["error"]))
+    dt, dv = [], []
+    for t in range(A.shape[0]):
+        fd.fit(A[t:t + 1])
+        v = fd.dump()
+        if v is not None:
+            dt.append(t)
+            dv.append(v[0] * np.sign(v[0][np.argmax(np.abs(v[0]))]))
+    assert dt == list(g["dumps_t"])
+    np.testing.assert_allclose(np.stack(dv), g["dumps_v"], rtol=0, atol=1e-9 * np.abs(g["dumps_v"]).max())
+    sketch, s2, vt, delta = fd.get()
+    np.testing.assert_allclose(s2, g["sigma2"], rtol=1e-9, atol=1e-12)
+    assert abs(delta - float(g["delta"])) <= 1e-9 * abs(float(g["delta"]))
+
+
+def test_oracle_rfd_batch_golden(golden_dir):
+    g = np.load(os.path.join(golden_dir, "rfd_batch.npz"))
+    A = g["A"].astype(np.float64)
+    r = so.RFD(A.shape[1], int(g["ell"]))
+    r.fit(A[:330], batch_size=12)
+    r.fit(A[330:], batch_size=5)
+    sketch, s2, vt, delta = r.get()
+    np.testing.assert_allclose(s2, g["sigma2"], rtol=1e-9)
+    np.testing.assert_allclose(sketch.T @ sketch, g["gram"], rtol=0, atol=1e-9 * np.abs(g["gram"]).max())
+    assert abs(delta - float(g["delta"])) <= 1e-9 * float(g["delta"])
+
+
+@pytest.mark.skipif(not ref_shim.available(), reason="reference tree not present (GPU box)")
+def test_oracle_bit_identical_to_live_reference():
+    swfd, mo, me = ref_shim.load()
+    rng = np.random.default_rng(7)
+    A = rng.standard_normal((400, 40)) * np.exp(0.5 * rng.standard_normal(400))[:, None]
+    R = float(np.max((A * A).sum(1)))
+    ref = swfd.SeqBasedSWFD(90, R, 40, 6)
+    ora = so.SeqSWFD(90, R, 40, 6)
+    for t in range(A.shape[0]):
+        ref.fit(A[t:t + 1])
+        ora.fit(A[t:t + 1])
+        if (t + 1) % 45 == 0:
+            a, b = ref.get(), ora.get()
+            assert all(np.array_equal(np.asarray(x), np.asarray(y)) for x, y in zip(a, b))
+            assert ref.get_size() == ora.get_size()
+
+
+@pytest.mark.skipif(not ref_shim.available(), reason="reference tree not present (GPU box)")
+def test_knn_adjacency_oracle_vs_reference_default_branch(capsys):
+    swfd, mo, me = ref_shim.load()
+    rng = np.random.default_rng(3)
+    F = rng.standard_normal((60, 7))
+    ref = mo.create_adjacency_matrix(F, "dense", k_basis=5)       # matrix_operations.py:112-130
+    adj, margin = ops_oracle.knn_adjacency(F, 5, "euclidean")
+    assert np.array_equal(ref.astype(np.uint8), adj)
+    a2 = mo.fuse_matrices([ref, ref.T])
+    assert np.array_equal(a2, ((ref + ref.T) > 0).astype(int))
+
+
+def test_cosine_assign_oracle_properties():
+    rng = np.random.default_rng(0)
+    C = rng.standard_normal((9, 33))
+    X = np.repeat(C, 3, axis=0) * rng.uniform(0.5, 2.0, size=(27, 1))      # scale invariance
+    labels, best, gap = ops_oracle.cosine_assign(X, C, 0.9)
+    assert np.array_equal(labels, np.repeat(np.arange(9), 3))
+    np.testing.assert_allclose(best, 1.0, atol=1e-12)
+    labels, _, _ = ops_oracle.cosine_assign(rng.standard_normal((50, 33)), C, 0.99)
+    assert np.all(labels == -1)
+    labels, best, _ = ops_oracle.cosine_assign(np.zeros((2, 33)), C, 0.0)    # zero rows: cosine 0
+    assert np.all(best == 0) and np.all(labels == 0)
