@@ -42,6 +42,9 @@ extern "C" {
 
 const char* mused_last_error(void);
 int mused_version(void);
+/* kernels launched by this library in this process so far (bench.py's gpu_launches) */
+uint64_t mused_launch_count(void);
+void mused_count_launches(uint64_t n);
 /* number of CUDA devices visible, or a negative error code */
 int mused_device_count(void);
 
@@ -99,6 +102,14 @@ int mused_swfd_time(mused_swfd_t* h, uint64_t* t);
 int mused_swfd_debug(mused_swfd_t* h, double* scal, double* sigma2, uint64_t* q_s,
                      uint64_t* q_t, int64_t q_cap);
 int mused_swfd_queue_capacity(mused_swfd_t* h, int64_t* q_cap);
+/* CUDA-event timing of the per-row kernel (the dominant kernel): returns the
+ * milliseconds, launches and rows accumulated since timing was last (re)armed,
+ * then enable = 1 arms and resets, 0 disarms and resets, -1 leaves the state alone. */
+int mused_swfd_timing(mused_swfd_t* h, int enable, double* ms, int64_t* launches, int64_t* rows);
+/* SM cycles the per-row kernel spent per phase, per physical FD instance:
+ * cycles[inst * 16 + k], k = {A bookkeeping, B gemv, C Q^T g, D deflate, E secular roots,
+ * F coupling vector, G eigenvector rows, H eigenvector GEMM, flush, dump, raw, rows} */
+int mused_swfd_profile(mused_swfd_t* h, uint64_t* cycles, int64_t n_inst_cap);
 
 /* ---------------------------------------------------------------------------
  * One Frequent Directions instance with row buffer and dump.

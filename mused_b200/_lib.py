@@ -32,7 +32,8 @@ _lib = None
 
 # every symbol include/mused_b200.h declares
 SYMBOLS = [
-    "mused_last_error", "mused_version", "mused_device_count",
+    "mused_last_error", "mused_version", "mused_device_count", "mused_launch_count",
+    "mused_count_launches", "mused_swfd_profile", "mused_swfd_timing",
     "mused_swfd_create", "mused_swfd_destroy", "mused_swfd_fit", "mused_swfd_get",
     "mused_swfd_size", "mused_swfd_time", "mused_swfd_debug", "mused_swfd_queue_capacity",
     "mused_fd_create", "mused_fd_destroy", "mused_fd_fit", "mused_fd_fit_batches",
@@ -52,6 +53,11 @@ def load():
     lib = C.CDLL(LIB_PATH)
     vp, i64, i32, dbl = C.c_void_p, C.c_int64, C.c_int32, C.c_double
     lib.mused_last_error.restype = C.c_char_p
+    lib.mused_launch_count.restype = C.c_uint64
+    lib.mused_count_launches.argtypes = [C.c_uint64]
+    lib.mused_count_launches.restype = None
+    lib.mused_swfd_profile.argtypes = [vp, vp, i64]
+    lib.mused_swfd_timing.argtypes = [vp, C.c_int, C.POINTER(dbl), C.POINTER(i64), C.POINTER(i64)]
     lib.mused_swfd_create.argtypes = [C.POINTER(vp), C.POINTER(SwfdCfg)]
     lib.mused_swfd_destroy.argtypes = [vp]
     lib.mused_swfd_fit.argtypes = [vp, vp, i64, i64, C.c_int, C.c_int, vp]

@@ -224,6 +224,7 @@ static int sm_count_of_current() {
 }  // namespace mused
 
 using namespace mused;
+extern "C" void mused_count_launches(uint64_t n);
 
 extern "C" {
 
@@ -243,6 +244,7 @@ int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float
     k_assign<<<grid, 256, 0, st>>>(X, n, d, ld_x, C, k, ld_c, cn2, metric, tau, labels, score);
     MUSED_CUDA(cudaGetLastError());
     MUSED_CUDA(cudaFreeAsync(cn2, st));
+    mused_count_launches(2);
     return 0;
 }
 
@@ -269,6 +271,7 @@ int mused_topk_adjacency(const float* feats, int64_t W, int64_t f, int64_t ld, i
     MUSED_CUDA(cudaGetLastError());
     MUSED_CUDA(cudaFreeAsync(S, st));
     MUSED_CUDA(cudaFreeAsync(n2, st));
+    mused_count_launches(3);
     return 0;
 }
 
@@ -283,6 +286,7 @@ int mused_contingency(const int32_t* prev, const int32_t* cur, int64_t n, int32_
     const int grid = (int)std::min<long long>((n + 255) / 256, 4ll * sm_count_of_current());
     k_contingency<<<grid, 256, 0, st>>>(prev, cur, n, P, Q, counts);
     MUSED_CUDA(cudaGetLastError());
+    mused_count_launches(1);
     return 0;
 }
 

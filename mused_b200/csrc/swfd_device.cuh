@@ -31,6 +31,7 @@ struct Slot {
     int n, b, rcur, qcur, q_ident, q_head, q_len;
     int f_reset, f_raw, f_flush, tail;
     int m, rot_n, parity, pad;
+    unsigned long long prof[16];  // cycles per phase, accumulated by the leader thread
 };
 
 enum { V_LAM = 0, V_LAMN, V_S2, V_G, V_W, V_DD, V_WW, V_WHAT, V_MU, NV };
@@ -87,6 +88,16 @@ struct Team {
     }
     __device__ __forceinline__ bool leader() const { return tid == 0; }
 };
+
+enum { PH_A = 0, PH_B, PH_C, PH_D, PH_E, PH_F, PH_G, PH_H, PH_FLUSH, PH_DUMP, PH_RAW, PH_ROWS, PH_N };
+#define PROF_MARK(ph)                                          \
+    do {                                                       \
+        if (T.leader()) {                                      \
+            const unsigned long long _now = clock64();         \
+            sl.prof[ph] += _now - t_prof;                      \
+            t_prof = _now;                                     \
+        }                                                      \
+    } while (0)
 
 struct TeamSmem {
     GemmSmem g[NWORK];
@@ -215,7 +226,7 @@ __device__ __forceinline__ int rank_sort_nd(int n, const double* val, const int*
 // ---------------------------------------------------------------------------
 template <int P>
 __device__ void fd_border(const Dev& D, int s, const Team<P>& T, TeamSmem& sm,
-                          const double* __restrict__ x, double alpha) {
+                          const double* __restrict__ x, double alpha, unsigned long long& t_prof) {
     Slot& sl = D.slots[s];
     const int n = sl.n, rcur = sl.rcur, qcur = sl.qcur;
     int q_ident = sl.q_ident;
@@ -256,6 +267,7 @@ __device__ void fd_border(const Dev& D, int s, const Team<P>& T, TeamSmem& sm,
         for (long long c = T.tid; c < d; c += T.nth) dst[c] = x[c];
     }
     T.sync();
+    PROF_MARK(PH_B);
 
     // ---- C: w = Q^T g --------------------------------------------------------
     if (q_ident) {
@@ -280,6 +292,7 @@ __device__ void fd_border(const Dev& D, int s, const Team<P>& T, TeamSmem& sm,
         }
     }
     T.sync();
+    PROF_MARK(PH_C);
 
     // ---- D: deflation + ordering (CTA 0) -------------------------------------
     if (T.rank == 0) {
@@ -350,6 +363,7 @@ __device__ void fd_border(const Dev& D, int s, const Team<P>& T, TeamSmem& sm,
         }
     }
     T.sync();
+    PROF_MARK(PH_D);
     const int m = sl.m;
     const int rot_n = sl.rot_n;
     const double wnorm = sl.wnorm;
@@ -393,6 +407,7 @@ __device__ void fd_border(const Dev& D, int s, const Team<P>& T, TeamSmem& sm,
         }
     }
     T.sync();
+    PROF_MARK(PH_E);
 
     // ---- F: coupling vector for which the roots are exact + sorted positions ---
     for (int i = T.wid; i < m; i += T.nw) {
@@ -422,6 +437,7 @@ __device__ void fd_border(const Dev& D, int s, const Team<P>& T, TeamSmem& sm,
         pos[slot] = cnt;
     }
     T.sync();
+    PROF_MARK(PH_F);
 
     // ---- G: eigenvector rows (transposed, already in sorted position) ----------
     for (int slot = T.wid; slot <= n; slot += T.nw) {
@@ -451,6 +467,7 @@ __device__ void fd_border(const Dev& D, int s, const Team<P>& T, TeamSmem& sm,
         if (T.lane == 0) lam[p] = lamn[slot];
     }
     T.sync();
+    PROF_MARK(PH_G);
 
     // ---- H: Q_new = diag(Q,1) * U  (rows of UT are eigenvectors) ---------------
     const int n1 = n + 1;
@@ -489,6 +506,7 @@ __device__ void fd_border(const Dev& D, int s, const Team<P>& T, TeamSmem& sm,
         sl.qcur = qcur ^ 1;
     }
     T.sync();
+    PROF_MARK(PH_H);
 }
 
 // ---------------------------------------------------------------------------
@@ -614,6 +632,7 @@ __global__ void __launch_bounds__(NT, 1) k_swfd_rows(Dev D, RowArgs A) {
         if (T.leader()) *A.out_flag = did ? 1 : 0;
         return;
     }
+    unsigned long long t_prof = clock64();
     for (long long r = 0; r < A.n_rows; ++r) {
         const double* x = A.rows + (size_t)r * D.d;
         const double nx = A.norm2[r];
@@ -669,6 +688,7 @@ __global__ void __launch_bounds__(NT, 1) k_swfd_rows(Dev D, RowArgs A) {
             }
         }
         T.sync();
+        PROF_MARK(PH_A);
         if (sl.f_reset) {
             double* R = D.Rp(s, sl.rcur);
             const size_t tot = (size_t)D.ell * D.d;
@@ -682,12 +702,14 @@ __global__ void __launch_bounds__(NT, 1) k_swfd_rows(Dev D, RowArgs A) {
             double* dst = D.ring_row(s, sl.tail);
             for (long long c = T.tid; c < D.d; c += T.nth) dst[c] = x[c];
             T.sync();
+            PROF_MARK(PH_RAW);
             continue;
         }
         const bool flush = sl.f_flush != 0;
-        fd_border<P>(D, s, T, sm, x, nx);
+        fd_border<P>(D, s, T, sm, x, nx, t_prof);
         if (flush) {
             fd_flush<P>(D, s, T, sm);
+            PROF_MARK(PH_FLUSH);
             if (A.mode == MODE_SEQ) {
                 // SlidingWindowFD.fit :126-130 / :134-138
                 const int tail = (sl.q_head + sl.q_len) % D.capn;
@@ -699,9 +721,11 @@ __global__ void __launch_bounds__(NT, 1) k_swfd_rows(Dev D, RowArgs A) {
                     sl.last_dump = t + 1ull;
                 }
                 T.sync();
+                PROF_MARK(PH_DUMP);
             }
         }
     }
+    if (T.leader()) sl.prof[PH_ROWS] += (unsigned long long)A.n_rows;
 }
 
 }  // namespace mused

@@ -11,6 +11,8 @@
 namespace mused {
 
 static thread_local std::string g_err;
+static unsigned long long g_launches = 0;
+#define COUNT_LAUNCH(n) (mused::g_launches += (n))
 void set_error(const char* fmt, ...) {
     char buf[1024];
     va_list ap;
@@ -274,6 +276,10 @@ struct Engine {
     int* o_flag = nullptr;
     std::vector<void*> allocs;
     int sm_count = 148;
+    bool timing = false;
+    std::vector<cudaEvent_t> ev;   // start/stop pairs around k_swfd_rows (MODE_SEQ/FD)
+    double timed_ms = 0.0;
+    long long timed_launches = 0, timed_rows = 0;
 
     template <class T>
     int alloc(T** p, size_t count) {
@@ -314,6 +320,7 @@ static int launch_rows(Engine& E, const RowArgs& A, int nslots, cudaStream_t st)
         case 8: MUSED_CUDA(cudaLaunchKernelEx(&cfg, k_swfd_rows<8>, E.D, A)); break;
         default: set_error("cluster must be 1, 2, 4 or 8"); return MUSED_ERR_ARG;
     }
+    COUNT_LAUNCH(1);
     return 0;
 }
 
@@ -442,6 +449,7 @@ static int stage_chunk(Engine& E, const void* dev_rows, long long n, long long l
         case MUSED_U8: k_stage_rows<unsigned char><<<(unsigned)n, 256, 0, st>>>((const unsigned char*)dev_rows, ld, d, E.stage, E.norm2); break;
     }
     MUSED_CUDA(cudaGetLastError());
+    COUNT_LAUNCH(1);
     return 0;
 }
 
@@ -482,8 +490,21 @@ static int engine_feed(Engine& E, const void* rows, long long n_rows, long long 
         A.slot0 = 0;
         A.batch = batch;
         A.last_call = (done + n == n_rows);
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (E.timing) {
+            MUSED_CUDA(cudaEventCreate(&e0));
+            MUSED_CUDA(cudaEventCreate(&e1));
+            MUSED_CUDA(cudaEventRecord(e0, st));
+        }
         rc = launch_rows(E, A, E.D.S, st);
         if (rc) return rc;
+        if (E.timing) {
+            MUSED_CUDA(cudaEventRecord(e1, st));
+            E.ev.push_back(e0);
+            E.ev.push_back(e1);
+            E.timed_launches += 1;
+            E.timed_rows += n;
+        }
         E.time += (unsigned long long)n;
         done += n;
         if (where == MUSED_HOST && done < n_rows) MUSED_CUDA(cudaStreamSynchronize(st));
@@ -524,6 +545,7 @@ static int engine_get(Engine& E, int s, bool merge, double* sketch, double* sigm
     if (!merge || sl.q_len == 0) {
         k_fd_out<<<E.sm_count, 256, 0, st>>>(D, s, E.o_sketch, E.o_s2, vt ? E.o_vt : nullptr, E.o_delta);
         MUSED_CUDA(cudaGetLastError());
+        COUNT_LAUNCH(1);
     } else {
         const int ng = D.ell + sl.q_len;
         const int nj = ng + (ng & 1);
@@ -557,6 +579,7 @@ static int engine_get(Engine& E, int s, bool merge, double* sketch, double* sigm
             E.M, ng, D.d, E.Vq, E.lda, E.perm, E.eval, D.ell, E.o_sketch, vt ? E.o_vt : nullptr, E.o_s2);
         MUSED_CUDA(cudaGetLastError());
         MUSED_CUDA(cudaMemsetAsync(E.o_delta, 0, sizeof(double), st));  // returns 0.0 (:171)
+        COUNT_LAUNCH(5);
     }
     if ((rc = copy_out(sketch, E.o_sketch, ld_out, where, st))) return rc;
     if ((rc = copy_out(sigma2, E.o_s2, (size_t)D.ell, where, st))) return rc;
@@ -576,6 +599,8 @@ struct mused_fd { Engine* E; };
 extern "C" {
 
 const char* mused_last_error(void) { return g_err.c_str(); }
+uint64_t mused_launch_count(void) { return g_launches; }
+void mused_count_launches(uint64_t n) { g_launches += n; }
 int mused_version(void) { return 100; }
 int mused_device_count(void) {
     int n = 0;
@@ -609,6 +634,44 @@ int mused_swfd_fit(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld
 int mused_swfd_time(mused_swfd_t* h, uint64_t* t) {
     MUSED_REQUIRE(h && t, "NULL argument");
     *t = h->E->time;
+    return 0;
+}
+int mused_swfd_profile(mused_swfd_t* h, uint64_t* cycles, int64_t n_inst_cap) {
+    MUSED_REQUIRE(h && cycles, "NULL argument");
+    std::vector<Slot> sl;
+    Engine& E = *h->E;
+    sl.resize(E.D.S);
+    if (E.D.S) {
+        MUSED_CUDA(cudaSetDevice(E.device));
+        MUSED_CUDA(cudaMemcpy(sl.data(), E.D.slots, sizeof(Slot) * E.D.S, cudaMemcpyDeviceToHost));
+    }
+    MUSED_REQUIRE(n_inst_cap >= E.D.S, "n_inst_cap too small");
+    for (int s = 0; s < E.D.S; ++s)
+        for (int k = 0; k < 16; ++k) cycles[(size_t)s * 16 + k] = sl[s].prof[k];
+    return 0;
+}
+int mused_swfd_timing(mused_swfd_t* h, int enable, double* ms, int64_t* launches, int64_t* rows) {
+    MUSED_REQUIRE(h, "NULL handle");
+    Engine& E = *h->E;
+    MUSED_CUDA(cudaSetDevice(E.device));
+    for (size_t i = 0; i + 1 < E.ev.size(); i += 2) {
+        float t = 0.f;
+        MUSED_CUDA(cudaEventSynchronize(E.ev[i + 1]));
+        MUSED_CUDA(cudaEventElapsedTime(&t, E.ev[i], E.ev[i + 1]));
+        E.timed_ms += t;
+        cudaEventDestroy(E.ev[i]);
+        cudaEventDestroy(E.ev[i + 1]);
+    }
+    E.ev.clear();
+    if (ms) *ms = E.timed_ms;
+    if (launches) *launches = E.timed_launches;
+    if (rows) *rows = E.timed_rows;
+    if (enable >= 0) {
+        E.timing = enable != 0;
+        E.timed_ms = 0.0;
+        E.timed_launches = 0;
+        E.timed_rows = 0;
+    }
     return 0;
 }
 int mused_swfd_queue_capacity(mused_swfd_t* h, int64_t* q) {

@@ -109,6 +109,22 @@ class SeqBasedSWFD:
                             n_dump=int(scal[o, 6]), n_raw=int(scal[o, 7])))
         return out
 
+    PHASES = ("A_book", "B_gemv", "C_QTg", "D_deflate", "E_roots", "F_what", "G_urows", "H_gemm",
+              "flush", "dump", "raw", "rows")
+
+    def profile(self):
+        """SM cycles per phase of the per-row kernel, per physical FD instance."""
+        S = max(1, 2 * len(self.thresholds))
+        buf = np.zeros((S, 16), dtype=np.uint64)
+        _lib.check(self._lib.mused_swfd_profile(self._h, buf.ctypes.data, S))
+        return [dict(zip(self.PHASES, (int(v) for v in row[:12]))) for row in buf[:2 * len(self.thresholds)]]
+
+    def kernel_timing(self, enable=-1):
+        """(ms, launches, rows) of the per-row kernel since timing was armed; enable=1 arms."""
+        ms, nl, nr = C.c_double(0.0), C.c_int64(0), C.c_int64(0)
+        _lib.check(self._lib.mused_swfd_timing(self._h, int(enable), C.byref(ms), C.byref(nl), C.byref(nr)))
+        return float(ms.value), int(nl.value), int(nr.value)
+
     def close(self):
         if getattr(self, "_h", None) is not None and self._h.value:
             self._lib.mused_swfd_destroy(self._h)
