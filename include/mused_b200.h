@@ -67,7 +67,19 @@ typedef struct {
     int32_t device;           /* CUDA ordinal                                            */
     int32_t cluster;          /* CTAs cooperating on one FD instance: 1,2,4,8; 0 = auto */
     int64_t chunk_rows;       /* rows staged per launch; 0 = auto                        */
+    int32_t schedule;         /* MUSED_SCHEDULE_REFERENCE | MUSED_SCHEDULE_BATCHED       */
+    int32_t batch_rows;       /* batched: rows per shrink (<= ell); 0 = ell              */
 } mused_swfd_cfg;
+
+/* REFERENCE: every flush / dump decision of the reference, row by row
+ * (frequent_directions.py:122-125) -- bit-faithful schedule, float64.
+ * BATCHED: north_star's schedule -- rows are folded in chunks of batch_rows with
+ * one tensor-core Gram + eigensolve + rotate per chunk and FD instance, every
+ * direction with sigma^2 >= threshold dumped per chunk (fastfdwithdump.py:115-131);
+ * stated exactly in oracle/swfd_batched_oracle.py.  fp32 rows, 3xTF32 products,
+ * float64 eigensolve and scalars. */
+#define MUSED_SCHEDULE_REFERENCE 0
+#define MUSED_SCHEDULE_BATCHED 1
 
 int mused_swfd_create(mused_swfd_t** out, const mused_swfd_cfg* cfg);
 int mused_swfd_destroy(mused_swfd_t* h);
@@ -106,6 +118,10 @@ int mused_swfd_queue_capacity(mused_swfd_t* h, int64_t* q_cap);
  * milliseconds, launches and rows accumulated since timing was last (re)armed,
  * then enable = 1 arms and resets, 0 disarms and resets, -1 leaves the state alone. */
 int mused_swfd_timing(mused_swfd_t* h, int enable, double* ms, int64_t* launches, int64_t* rows);
+/* batched schedule: CUDA-event milliseconds per kernel class since timing was armed,
+ * ms5 = {K1 stage, K5 bookkeeping, K2 Gram, K3 eigensolve, K4 rotate}; chunks and rows
+ * folded meanwhile.  enable as in mused_swfd_timing. */
+int mused_swfd_kernel_ms(mused_swfd_t* h, int enable, double* ms5, int64_t* chunks, int64_t* rows);
 /* SM cycles the per-row kernel spent per phase, per physical FD instance:
  * cycles[inst * 16 + k], k = {A bookkeeping, B gemv, C Q^T g, D deflate, E secular roots,
  * F coupling vector, G eigenvector rows, H eigenvector GEMM, flush, dump, raw, rows} */

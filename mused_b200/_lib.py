@@ -25,7 +25,11 @@ _NP_DTYPES = {np.dtype(np.float64): F64, np.dtype(np.float32): F32, np.dtype(np.
 class SwfdCfg(C.Structure):
     _fields_ = [("N", C.c_int64), ("d", C.c_int64), ("ell", C.c_int64), ("beta", C.c_double),
                 ("n_levels", C.c_int32), ("thresholds", C.POINTER(C.c_double)),
-                ("device", C.c_int32), ("cluster", C.c_int32), ("chunk_rows", C.c_int64)]
+                ("device", C.c_int32), ("cluster", C.c_int32), ("chunk_rows", C.c_int64),
+                ("schedule", C.c_int32), ("batch_rows", C.c_int32)]
+
+
+SCHEDULES = {"reference": 0, "batched": 1}
 
 
 _lib = None
@@ -33,7 +37,7 @@ _lib = None
 # every symbol include/mused_b200.h declares
 SYMBOLS = [
     "mused_last_error", "mused_version", "mused_device_count", "mused_launch_count",
-    "mused_count_launches", "mused_swfd_profile", "mused_swfd_timing",
+    "mused_count_launches", "mused_swfd_profile", "mused_swfd_timing", "mused_swfd_kernel_ms",
     "mused_swfd_create", "mused_swfd_destroy", "mused_swfd_fit", "mused_swfd_get",
     "mused_swfd_size", "mused_swfd_time", "mused_swfd_debug", "mused_swfd_queue_capacity",
     "mused_fd_create", "mused_fd_destroy", "mused_fd_fit", "mused_fd_fit_batches",
@@ -58,6 +62,7 @@ def load():
     lib.mused_count_launches.restype = None
     lib.mused_swfd_profile.argtypes = [vp, vp, i64]
     lib.mused_swfd_timing.argtypes = [vp, C.c_int, C.POINTER(dbl), C.POINTER(i64), C.POINTER(i64)]
+    lib.mused_swfd_kernel_ms.argtypes = [vp, C.c_int, C.POINTER(dbl), C.POINTER(i64), C.POINTER(i64)]
     lib.mused_swfd_create.argtypes = [C.POINTER(vp), C.POINTER(SwfdCfg)]
     lib.mused_swfd_destroy.argtypes = [vp]
     lib.mused_swfd_fit.argtypes = [vp, vp, i64, i64, C.c_int, C.c_int, vp]

@@ -1,0 +1,725 @@
+// Batched-schedule SWFD engine (north_star's form of the path): the stream is cut
+// into chunks of <= l rows; per chunk every FD instance of the level ladder runs
+//   K1  k_bstage    rows (any dtype) -> TF32 hi/lo planes of the shared chunk + ||x||^2
+//   K5  k_bbook     period swap, snapshot expiry / cap trim, raw-row snapshots, masks
+//   K2  k_gram_tc   G = [sketch; chunk][sketch; chunk]^T          (tcgen05, gram_tc.cuh)
+//   K3  k_eig_jacobi  eig(G), shrink, dump decisions                (eig_jacobi.cuh)
+//   K4  k_brotate   sketch' = T [sketch; chunk], dumped rows -> snapshot ring
+// with no host synchronisation between chunks.  The schedule and its arithmetic
+// are stated in oracle/swfd_batched_oracle.py; reference lines:
+//   swfd/seq_based_swfd.py:47-103, swfd/sliding_windows_frequent_directions.py:56-173,
+//   swfd/frequent_directions.py:39-58,86-93, swfd/fastfdwithdump.py:115-131.
+#include <math.h>
+#include <algorithm>
+#include <vector>
+
+#include "bswfd.h"
+#include "gram_tc.cuh"
+
+namespace mused {
+
+// ---------------------------------------------------------------------------
+// K1: stage rows [row_off, row_off + m) of the chunk.  One CTA per row, fixed
+// reduction order for ||x||^2 (it decides routing, seq_based_swfd.py:76-77).
+// ---------------------------------------------------------------------------
+template <class Tin>
+__global__ void __launch_bounds__(256) k_bstage(const Tin* __restrict__ in, long long ld, long long d,
+                                                int row_off, float* __restrict__ xhi,
+                                                float* __restrict__ xlo, double* __restrict__ norm2) {
+    __shared__ double red[8];
+    const int r = blockIdx.x;
+    const Tin* src = in + (size_t)r * ld;
+    float* hi = xhi + (size_t)(row_off + r) * d;
+    float* lo = xlo + (size_t)(row_off + r) * d;
+    double acc = 0.0;
+    for (long long c = threadIdx.x; c < d; c += 256) {
+        const float v = (float)src[c];
+        float h, l;
+        umma::split_tf32(v, h, l);
+        hi[c] = h;
+        lo[c] = l;
+        acc = fma((double)v, (double)v, acc);
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int i = 0; i < 8; ++i) t += red[i];
+        norm2[row_off + r] = t;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// K5: per-instance bookkeeping of one chunk (times t_a .. t_a + n - 1).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_bbook(BDev D, int n, unsigned long long t_a) {
+    __shared__ int raw_row[BS_MAX_ELL], raw_slot[BS_MAX_ELL];
+    __shared__ int n_raw_s, do_reset;
+    const int s = blockIdx.x;
+    BSlot& sl = D.slots[s];
+    const unsigned long long t_b = t_a + (unsigned long long)n - 1ull;
+    unsigned long long* qs = D.ringS + (size_t)s * D.capn;
+    unsigned long long* qt = D.ringT + (size_t)s * D.capn;
+    if (threadIdx.x == 0) {
+        int reset = 0;
+        const unsigned long long p = t_a / D.N;
+        if (p > sl.period) {                       // sliding_windows_frequent_directions.py:99-107
+            sl.period = p;
+            if ((int)(p & 1ull) != sl.parity) {    // this slot becomes the fresh fd_aux
+                reset = 1;
+                sl.delta = 0.0;
+                sl.q_head = 0;
+                sl.q_len = 0;
+                sl.last_dump = t_a;
+                sl.n_flush = 0;
+                sl.n_dump = 0;
+                sl.n_raw = 0;
+            }
+        }
+        int head = sl.q_head, len = sl.q_len;
+        while (len > 0 && ((double)len > D.qcap || qt[head] + D.N <= t_b)) {   // seq_based_swfd.py:59-74
+            head = (head + 1) % D.capn;
+            --len;
+        }
+        int nr = 0;
+        unsigned long long last = sl.last_dump;
+        const double thr = sl.error;
+        for (int r = 0; r < n; ++r) {
+            if (D.norm2[r] >= thr) {               // :76-77 -> SlidingWindowFD.append (:56-80)
+                if (len == D.capn) { head = (head + 1) % D.capn; --len; sl.overflow += 1; }
+                const int tail = (head + len) % D.capn;
+                qs[tail] = last;
+                qt[tail] = t_a + (unsigned long long)r;
+                last = t_a + (unsigned long long)r + 1ull;
+                ++len;
+                raw_row[nr] = r;
+                raw_slot[nr] = tail;
+                ++nr;
+            }
+        }
+        sl.q_head = head;
+        sl.q_len = len;
+        sl.last_dump = last;
+        sl.n_raw += (unsigned long long)nr;
+        sl.npend = n - nr;
+        n_raw_s = nr;
+        do_reset = reset;
+    }
+    __syncthreads();
+    unsigned char* mk = D.mask + (size_t)s * D.ell;
+    for (int r = threadIdx.x; r < D.ell; r += 256) mk[r] = 0;
+    __syncthreads();
+    const int nr = n_raw_s;
+    for (int k = threadIdx.x; k < nr; k += 256) mk[raw_row[k]] = 1;
+    if (do_reset) {
+        const size_t off = ((size_t)s * 2 + sl.cur) * D.ell * D.d;
+        const size_t tot = (size_t)D.ell * D.d;
+        for (size_t e = threadIdx.x; e < tot; e += 256) {
+            D.skhi[off + e] = 0.f;
+            D.sklo[off + e] = 0.f;
+        }
+        for (int i = threadIdx.x; i < D.ell; i += 256) D.s2[(size_t)s * D.ell + i] = 0.0;
+    }
+    for (int k = 0; k < nr; ++k) {
+        const float* h = D.xhi + (size_t)raw_row[k] * D.d;
+        const float* l = D.xlo + (size_t)raw_row[k] * D.d;
+        float* dst = D.ringV + ((size_t)s * D.capn + raw_slot[k]) * D.d;
+        for (long long c = threadIdx.x; c < D.d; c += 256) dst[c] = h[c] + l[c];
+    }
+}
+
+// ---------------------------------------------------------------------------
+// K4: shrink + rotate (frequent_directions.py:86-93, :58):
+//   out[r][c] = sum_k T[r][k] * R[k][c],  R = [sketch(src plane); chunk]
+// 64 x 64 output tile per CTA, fp32 FMA on the exact hi + lo values.  Rows whose
+// direction is dumped (fastfdwithdump.py:115-131) go to their snapshot-ring
+// entry instead and leave a zero row in the sketch.
+// ---------------------------------------------------------------------------
+constexpr int RT = 64, RK = 16;
+__global__ void __launch_bounds__(256) k_brotate(BDev D) {
+    __shared__ float sa[RK][RT + 4];
+    __shared__ float sb[RK][RT + 4];
+    const int s = blockIdx.z;
+    const BSlot& sl = D.slots[s];
+    if (sl.skip) return;
+    const int ell = D.ell, n2 = D.n2;
+    const long long d = D.d;
+    const int r0 = blockIdx.y * RT;
+    const long long c0 = (long long)blockIdx.x * RT;
+    const int src = sl.src;
+    const float* Ts = D.T + (size_t)s * ell * n2;
+    const float* skh = D.skhi + ((size_t)s * 2 + src) * ell * d;
+    const float* skl = D.sklo + ((size_t)s * 2 + src) * ell * d;
+    const int t = threadIdx.x, ty = t >> 4, tx = t & 15;
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    for (int k0 = 0; k0 < n2; k0 += RK) {
+#pragma unroll
+        for (int e = t; e < RT * RK; e += 256) {
+            const int kk = e & (RK - 1), mm = e >> 4;          // T: k contiguous
+            const int r = r0 + mm;
+            sa[kk][mm] = (r < ell) ? Ts[(size_t)r * n2 + k0 + kk] : 0.f;
+            const int nn = e & (RT - 1), kb = e >> 6;          // R: c contiguous
+            const int k = k0 + kb;
+            const long long c = c0 + nn;
+            float v = 0.f;
+            if (c < d) {
+                if (k < ell) v = skh[(size_t)k * d + c] + skl[(size_t)k * d + c];
+                else v = D.xhi[(size_t)(k - ell) * d + c] + D.xlo[(size_t)(k - ell) * d + c];
+            }
+            sb[kb][nn] = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < RK; ++kk) {
+            float av[4], bv[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) av[i] = sa[kk][ty * 4 + i];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) bv[j] = sb[kk][tx * 4 + j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+    float* dh = D.skhi + ((size_t)s * 2 + (src ^ 1)) * ell * d;
+    float* dl = D.sklo + ((size_t)s * 2 + (src ^ 1)) * ell * d;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int r = r0 + ty * 4 + i;
+        if (r >= ell) continue;
+        const int ds = D.dump_slot[(size_t)s * ell + r];
+        float* ring = ds >= 0 ? D.ringV + ((size_t)s * D.capn + ds) * d : nullptr;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const long long c = c0 + tx * 4 + j;
+            if (c >= d) continue;
+            float h = 0.f, l = 0.f;
+            if (ring) ring[c] = acc[i][j];
+            else umma::split_tf32(acc[i][j], h, l);
+            dh[(size_t)r * d + c] = h;
+            dl[(size_t)r * d + c] = l;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Query support: float64 stack [sketch; live snapshots] of one instance, and the
+// plain FD output (sketch, sigma^2, Vt = sketch / sqrt(sigma^2), delta).
+// ---------------------------------------------------------------------------
+__global__ void k_bgather(BDev D, int s, double* __restrict__ M) {
+    const BSlot& sl = D.slots[s];
+    const int rows = D.ell + sl.q_len;
+    const float* skh = D.skhi + ((size_t)s * 2 + sl.cur) * D.ell * D.d;
+    const float* skl = D.sklo + ((size_t)s * 2 + sl.cur) * D.ell * D.d;
+    for (int i = blockIdx.x; i < rows; i += gridDim.x) {
+        double* dst = M + (size_t)i * D.d;
+        if (i < D.ell) {
+            for (long long c = threadIdx.x; c < D.d; c += blockDim.x)
+                dst[c] = (double)skh[(size_t)i * D.d + c] + (double)skl[(size_t)i * D.d + c];
+        } else {
+            const float* src = D.ringV + ((size_t)s * D.capn + (sl.q_head + (i - D.ell)) % D.capn) * D.d;
+            for (long long c = threadIdx.x; c < D.d; c += blockDim.x) dst[c] = (double)src[c];
+        }
+    }
+}
+
+__global__ void k_bfd_out(BDev D, int s, double* sketch, double* sigma2, double* vt, double* delta) {
+    const BSlot& sl = D.slots[s];
+    const float* skh = D.skhi + ((size_t)s * 2 + sl.cur) * D.ell * D.d;
+    const float* skl = D.sklo + ((size_t)s * 2 + sl.cur) * D.ell * D.d;
+    const double* s2 = D.s2 + (size_t)s * D.ell;
+    const size_t tot = (size_t)D.ell * D.d;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < tot; e += (size_t)gridDim.x * blockDim.x) {
+        const int i = (int)(e / D.d);
+        const double v = (double)skh[e] + (double)skl[e];
+        sketch[e] = v;
+        if (vt) vt[e] = (s2[i] > 0.0) ? v / sqrt(s2[i]) : 0.0;
+    }
+    if (blockIdx.x == 0) {
+        for (int i = threadIdx.x; i < D.ell; i += blockDim.x) sigma2[i] = s2[i];
+        if (threadIdx.x == 0) *delta = sl.delta;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Engine
+// ---------------------------------------------------------------------------
+struct BEngine {
+    BDev D{};
+    int device = 0, n_levels = 0, sm_count = 148;
+    long long batch = 0;
+    unsigned long long time = 0;      // rows handed to fit()
+    unsigned long long done = 0;      // rows folded into the state
+    int pend = 0;                     // rows staged in the chunk planes, not yet processed
+    CUtensorMap tm_sk_hi, tm_sk_lo, tm_x_hi, tm_x_lo;
+    unsigned char* raw = nullptr;     // H2D staging of caller rows
+    size_t raw_bytes = 0;
+    QueryScratch Q;
+    double *o_sketch = nullptr, *o_vt = nullptr, *o_s2 = nullptr, *o_delta = nullptr;
+    std::vector<void*> allocs;
+    bool timing = false;
+    std::vector<cudaEvent_t> ev[5];
+    double timed_ms[5] = {0, 0, 0, 0, 0};
+    long long timed_chunks = 0, timed_rows = 0;
+
+    template <class T>
+    int alloc(T** p, size_t count) {
+        void* q = nullptr;
+        cudaError_t e = cudaMalloc(&q, count * sizeof(T));
+        if (e != cudaSuccess) {
+            set_error("cudaMalloc of %zu bytes failed: %s", count * sizeof(T), cudaGetErrorString(e));
+            return MUSED_ERR_NOMEM;
+        }
+        e = cudaMemset(q, 0, count * sizeof(T));
+        if (e != cudaSuccess) { set_error("cudaMemset failed: %s", cudaGetErrorString(e)); return MUSED_ERR_CUDA; }
+        allocs.push_back(q);
+        *p = (T*)q;
+        return 0;
+    }
+    ~BEngine() {
+        for (int k = 0; k < 5; ++k)
+            for (cudaEvent_t e : ev[k]) cudaEventDestroy(e);
+        for (void* p : allocs) cudaFree(p);
+    }
+    void mark(int k, cudaStream_t st) {
+        if (!timing) return;
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        cudaEventRecord(e, st);
+        ev[k].push_back(e);
+    }
+};
+
+extern "C" void mused_count_launches(uint64_t n);
+
+static size_t b_dtype_size(int dt) {
+    switch (dt) {
+        case MUSED_F64: case MUSED_I64: return 8;
+        case MUSED_F32: case MUSED_I32: return 4;
+        case MUSED_U8: return 1;
+    }
+    return 0;
+}
+
+int bengine_create(BEngine** out, long long N, long long d, long long ell, double beta, int n_levels,
+                   const double* thr, int device, long long batch) {
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0) {
+        set_error("no CUDA device available (%s); mused_b200 has no CPU fallback",
+                  ce != cudaSuccess ? cudaGetErrorString(ce) : "device count is 0");
+        return MUSED_ERR_CUDA;
+    }
+    MUSED_REQUIRE(device >= 0 && device < ndev, "device %d out of range (have %d)", device, ndev);
+    MUSED_REQUIRE(ell == 16 || ell == 32 || ell == 64 || ell == 128,
+                  "schedule=batched supports sketch_dim 16, 32, 64 or 128 (got %lld); use schedule=reference", ell);
+    MUSED_REQUIRE(d % 32 == 0 && d > ell, "schedule=batched needs d %% 32 == 0 and d > sketch_dim (d=%lld)", d);
+    MUSED_REQUIRE(N >= 1 && beta > 0, "bad N / beta");
+    MUSED_REQUIRE(n_levels >= 0 && n_levels <= 64, "n_levels out of range");
+    if (batch <= 0) batch = ell;
+    MUSED_REQUIRE(batch <= ell, "batch_rows must be <= sketch_dim");
+    MUSED_CUDA(cudaSetDevice(device));
+    BEngine* E = new BEngine();
+    E->device = device;
+    E->n_levels = n_levels;
+    E->batch = batch;
+    cudaDeviceProp prop;
+    MUSED_CUDA(cudaGetDeviceProperties(&prop, device));
+    E->sm_count = prop.multiProcessorCount;
+    BDev& D = E->D;
+    const int S = 2 * n_levels;
+    D.S = S;
+    D.ell = (int)ell;
+    D.n2 = 2 * (int)ell;
+    D.d = d;
+    D.N = (unsigned long long)N;
+    D.qcap = (2.0 + 8.0 / beta) * (double)ell;
+    D.capn = (int)floor(D.qcap) + (int)batch + (int)ell + 2;
+    // split-K: enough CTAs to cover the SMs, K slices of whole 32-float blocks
+    int KS = 16;
+    while (KS > 1 && (d % (32 * KS) != 0 || (long long)S * KS > 2LL * E->sm_count)) KS >>= 1;
+    D.KS = KS;
+    int rc = 0;
+#define A_(p, n) if ((rc = E->alloc(&(p), (n))) != 0) { delete E; return rc; }
+    const size_t Sa = (size_t)std::max(S, 1);
+    A_(D.slots, Sa);
+    A_(D.skhi, Sa * 2 * ell * d);
+    A_(D.sklo, Sa * 2 * ell * d);
+    A_(D.xhi, (size_t)ell * d);
+    A_(D.xlo, (size_t)ell * d);
+    A_(D.norm2, (size_t)ell);
+    A_(D.mask, Sa * ell);
+    A_(D.Gp, Sa * KS * D.n2 * D.n2);
+    A_(D.T, Sa * ell * D.n2);
+    A_(D.s2, Sa * ell);
+    A_(D.dump_slot, Sa * ell);
+    A_(D.ringV, Sa * D.capn * d);
+    A_(D.ringS, Sa * D.capn);
+    A_(D.ringT, Sa * D.capn);
+    E->raw_bytes = (size_t)std::max<long long>(ell, std::min<long long>(8192, (64ll << 20) / (d * 8))) * d * 8;
+    A_(E->raw, E->raw_bytes);
+    QueryScratch& Q = E->Q;
+    Q.ng_max = D.ell + D.capn + 1;
+    Q.ng_max += Q.ng_max & 1;
+    Q.lda = Q.ng_max;
+    A_(Q.M, (size_t)Q.ng_max * d);
+    A_(Q.G, (size_t)Q.lda * Q.lda);
+    A_(Q.Vq, (size_t)Q.lda * Q.lda);
+    A_(Q.cs, (size_t)Q.ng_max);
+    A_(Q.eval, (size_t)Q.ng_max);
+    A_(Q.perm, (size_t)Q.ng_max);
+    A_(Q.counters, 64);
+    A_(Q.scr, 8);
+    A_(E->o_sketch, (size_t)ell * d);
+    A_(E->o_vt, (size_t)ell * d);
+    A_(E->o_s2, (size_t)ell);
+    A_(E->o_delta, 1);
+#undef A_
+    std::vector<BSlot> init(Sa);
+    memset(init.data(), 0, sizeof(BSlot) * Sa);
+    for (int s = 0; s < S; ++s) {
+        init[s].error = thr[s / 2];
+        init[s].last_dump = 1;       // sliding_windows_frequent_directions.py:23
+        init[s].parity = s & 1;
+        init[s].skip = 1;
+    }
+    MUSED_CUDA(cudaMemcpy(D.slots, init.data(), sizeof(BSlot) * Sa, cudaMemcpyHostToDevice));
+    CUresult r1 = encode_tmap_f32_2d(&E->tm_sk_hi, D.skhi, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
+    CUresult r2 = encode_tmap_f32_2d(&E->tm_sk_lo, D.sklo, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
+    CUresult r3 = encode_tmap_f32_2d(&E->tm_x_hi, D.xhi, (uint64_t)ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
+    CUresult r4 = encode_tmap_f32_2d(&E->tm_x_lo, D.xlo, (uint64_t)ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
+    if (r1 != CUDA_SUCCESS || r2 != CUDA_SUCCESS || r3 != CUDA_SUCCESS || r4 != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (%d %d %d %d)", (int)r1, (int)r2, (int)r3, (int)r4);
+        delete E;
+        return MUSED_ERR_CUDA;
+    }
+    *out = E;
+    return 0;
+}
+
+void bengine_destroy(BEngine* E) {
+    if (!E) return;
+    cudaSetDevice(E->device);
+    delete E;
+}
+
+template <int N2>
+static int launch_gram(BEngine& E, cudaStream_t st) {
+    using C = GramCfg<N2>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        MUSED_CUDA(cudaFuncSetAttribute(k_gram_tc<N2>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        attr_set = true;
+    }
+    GramArgs A;
+    A.slots = E.D.slots;
+    A.Gp = E.D.Gp;
+    A.ell = E.D.ell;
+    A.KS = E.D.KS;
+    A.kblocks = (int)(E.D.d / (32 * E.D.KS));
+    k_gram_tc<N2><<<dim3(E.D.KS, E.D.S), 192, C::SMEM_BYTES, st>>>(E.tm_sk_hi, E.tm_sk_lo, E.tm_x_hi, E.tm_x_lo, A);
+    MUSED_CUDA(cudaGetLastError());
+    return 0;
+}
+
+template <int EPL>
+static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t st) {
+    static bool attr_set = false;
+    const int smem = (int)sizeof(EigSmem<EPL>);
+    if (!attr_set) {
+        MUSED_CUDA(cudaFuncSetAttribute(k_eig_jacobi<EPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set = true;
+    }
+    EigArgs A;
+    A.slots = E.D.slots;
+    A.Gp = E.D.Gp;
+    A.KS = E.D.KS;
+    A.ell = E.D.ell;
+    A.n2 = E.D.n2;
+    A.capn = E.D.capn;
+    A.mask = E.D.mask;
+    A.n_rows = n;
+    A.t_end = t_end;
+    A.T = E.D.T;
+    A.s2 = E.D.s2;
+    A.dump_slot = E.D.dump_slot;
+    A.ringS = E.D.ringS;
+    A.ringT = E.D.ringT;
+    A.tol = 1e-4;          // quadratic phase: the sweep that measures <= 1e-4 leaves ~1e-8
+    A.max_sweeps = 24;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(E.D.S * EPL));
+    cfg.blockDim = dim3(EIG_NT);
+    cfg.dynamicSmemBytes = (size_t)smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = EPL;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    MUSED_CUDA(cudaLaunchKernelEx(&cfg, k_eig_jacobi<EPL>, A));
+    return 0;
+}
+
+// fold the staged chunk (E.pend rows, times done+1 ..) into every FD instance
+static int process_chunk(BEngine& E, cudaStream_t st) {
+    const int n = E.pend;
+    if (n == 0) return 0;
+    BDev& D = E.D;
+    const unsigned long long t_a = E.done + 1ull;
+    int rc = 0;
+    if (D.S > 0) {
+        E.mark(1, st);
+        k_bbook<<<D.S, 256, 0, st>>>(D, n, t_a);
+        MUSED_CUDA(cudaGetLastError());
+        E.mark(1, st);
+        E.mark(2, st);
+        switch (D.ell) {
+            case 16: rc = launch_gram<32>(E, st); break;
+            case 32: rc = launch_gram<64>(E, st); break;
+            case 64: rc = launch_gram<128>(E, st); break;
+            default: rc = launch_gram<256>(E, st); break;
+        }
+        if (rc) return rc;
+        E.mark(2, st);
+        E.mark(3, st);
+        const unsigned long long t_end = t_a + (unsigned long long)n - 1ull;
+        switch (D.ell) {
+            case 16: rc = launch_eig<1>(E, n, t_end, st); break;
+            case 32: rc = launch_eig<2>(E, n, t_end, st); break;
+            case 64: rc = launch_eig<4>(E, n, t_end, st); break;
+            default: rc = launch_eig<8>(E, n, t_end, st); break;
+        }
+        if (rc) return rc;
+        E.mark(3, st);
+        E.mark(4, st);
+        k_brotate<<<dim3((unsigned)((D.d + RT - 1) / RT), (unsigned)((D.ell + RT - 1) / RT), (unsigned)D.S), 256, 0, st>>>(D);
+        MUSED_CUDA(cudaGetLastError());
+        E.mark(4, st);
+        mused_count_launches(4);
+    }
+    if (E.timing) { E.timed_chunks += 1; E.timed_rows += n; }
+    E.done += (unsigned long long)n;
+    E.pend = 0;
+    return 0;
+}
+
+// rows the current chunk may still take before it must be processed
+static long long chunk_room(const BEngine& E) {
+    const unsigned long long t_a = E.done + 1ull;
+    const unsigned long long N = E.D.N;
+    const unsigned long long to_boundary = (t_a % N) ? N - (t_a % N) : N;   // rows until the next multiple of N
+    const long long cap = (long long)std::min<unsigned long long>((unsigned long long)E.batch, to_boundary);
+    return cap - E.pend;
+}
+
+static int stage_rows(BEngine& E, const void* dev_rows, long long m, long long ld, int dtype, cudaStream_t st) {
+    BDev& D = E.D;
+    E.mark(0, st);
+    switch (dtype) {
+        case MUSED_F64: k_bstage<double><<<(unsigned)m, 256, 0, st>>>((const double*)dev_rows, ld, D.d, E.pend, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_F32: k_bstage<float><<<(unsigned)m, 256, 0, st>>>((const float*)dev_rows, ld, D.d, E.pend, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_I64: k_bstage<long long><<<(unsigned)m, 256, 0, st>>>((const long long*)dev_rows, ld, D.d, E.pend, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_I32: k_bstage<int><<<(unsigned)m, 256, 0, st>>>((const int*)dev_rows, ld, D.d, E.pend, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_U8: k_bstage<unsigned char><<<(unsigned)m, 256, 0, st>>>((const unsigned char*)dev_rows, ld, D.d, E.pend, D.xhi, D.xlo, D.norm2); break;
+    }
+    MUSED_CUDA(cudaGetLastError());
+    E.mark(0, st);
+    mused_count_launches(1);
+    E.pend += (int)m;
+    return 0;
+}
+
+int bengine_fit(BEngine* Ep, const void* rows, long long n_rows, long long ld, int dtype, int where,
+                cudaStream_t st) {
+    BEngine& E = *Ep;
+    const size_t es = b_dtype_size(dtype);
+    MUSED_REQUIRE(es != 0, "unknown dtype %d", dtype);
+    MUSED_REQUIRE(n_rows >= 0 && ld >= E.D.d, "bad shape: n_rows=%lld ld=%lld d=%lld", n_rows, ld, E.D.d);
+    MUSED_REQUIRE(rows != nullptr || n_rows == 0, "rows is NULL");
+    MUSED_CUDA(cudaSetDevice(E.device));
+    const long long d = E.D.d;
+    const long long host_rows = (long long)(E.raw_bytes / ((size_t)d * es));
+    long long fed = 0;
+    while (fed < n_rows) {
+        // a block of caller rows that is resident on the device
+        long long blk = n_rows - fed;
+        const char* src = (const char*)rows + (size_t)fed * ld * es;
+        const void* dev = src;
+        long long dev_ld = ld;
+        if (where == MUSED_HOST) {
+            blk = std::min(blk, host_rows);
+            if (ld == d) MUSED_CUDA(cudaMemcpyAsync(E.raw, src, (size_t)blk * d * es, cudaMemcpyHostToDevice, st));
+            else MUSED_CUDA(cudaMemcpy2DAsync(E.raw, (size_t)d * es, src, (size_t)ld * es, (size_t)d * es, (size_t)blk, cudaMemcpyHostToDevice, st));
+            dev = E.raw;
+            dev_ld = d;
+        }
+        long long off = 0;
+        while (off < blk) {
+            const long long m = std::min(blk - off, chunk_room(E));
+            int rc = stage_rows(E, (const char*)dev + (size_t)off * dev_ld * es, m, dev_ld, dtype, st);
+            if (rc) return rc;
+            off += m;
+            E.time += (unsigned long long)m;
+            if (chunk_room(E) == 0) {
+                rc = process_chunk(E, st);
+                if (rc) return rc;
+            }
+        }
+        fed += blk;
+        if (where == MUSED_HOST) MUSED_CUDA(cudaStreamSynchronize(st));   // E.raw is reused / caller buffer is free
+    }
+    return 0;
+}
+
+unsigned long long bengine_time(BEngine* E) { return E->time; }
+int bengine_qcap(BEngine* E) { return E->D.capn; }
+
+static int b_read_slots(BEngine& E, std::vector<BSlot>& sl) {
+    sl.resize(std::max(E.D.S, 1));
+    MUSED_CUDA(cudaSetDevice(E.device));
+    MUSED_CUDA(cudaMemcpy(sl.data(), E.D.slots, sizeof(BSlot) * sl.size(), cudaMemcpyDeviceToHost));
+    return 0;
+}
+static int b_fd_slot(const BEngine& E, int level) {
+    // the chunk that contains row `done` decided the period: period = t_a / N of the last chunk;
+    // rows are only folded in whole chunks, so done / N is that period once a boundary row was folded
+    const unsigned long long p = E.done / E.D.N;
+    return 2 * level + (int)(p & 1ull);
+}
+
+int bengine_size(BEngine* E, long long* n) {
+    std::vector<BSlot> sl;
+    int rc = b_read_slots(*E, sl);
+    if (rc) return rc;
+    long long tot = 0;
+    for (int j = 0; j < E->n_levels; ++j) tot += sl[2 * j].q_len + sl[2 * j + 1].q_len + 2ll * E->D.ell;
+    *n = tot;
+    return 0;
+}
+
+static int b_copy_out(double* dst, const double* src, size_t n, int where, cudaStream_t st) {
+    if (!dst) return 0;
+    MUSED_CUDA(cudaMemcpyAsync(dst, src, n * sizeof(double),
+                               where == MUSED_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
+
+int bengine_get(BEngine* Ep, double* sketch, double* sigma2, double* vt, double* delta, int* level,
+                int where, cudaStream_t st) {
+    BEngine& E = *Ep;
+    BDev& D = E.D;
+    if (E.n_levels == 0) {
+        set_error("SeqBasedSWFD has zero levels (R <= 1): get() is undefined");
+        return MUSED_ERR_STATE;
+    }
+    MUSED_CUDA(cudaSetDevice(E.device));
+    int rc = process_chunk(E, st);      // get() closes the open chunk (the reference flushes on get, too)
+    if (rc) return rc;
+    MUSED_CUDA(cudaStreamSynchronize(st));
+    std::vector<BSlot> sl;
+    if ((rc = b_read_slots(E, sl))) return rc;
+    int rj = 0;
+    const unsigned long long time = E.time, N = D.N;
+    for (int j = 0; j < E.n_levels; ++j) {        // seq_based_swfd.py:83-98
+        const int s = b_fd_slot(E, j);
+        if (sl[s].q_len == 0) break;
+        unsigned long long head_s = 0;
+        MUSED_CUDA(cudaMemcpy(&head_s, D.ringS + (size_t)s * D.capn + sl[s].q_head, 8, cudaMemcpyDeviceToHost));
+        if (time - head_s >= std::min(N - 1ull, time - 1ull)) { rj = j; break; }
+    }
+    if (level) *level = rj;
+    const int s = b_fd_slot(E, rj);
+    const size_t ld_out = (size_t)D.ell * D.d;
+    if (sl[s].q_len == 0) {
+        k_bfd_out<<<E.sm_count, 256, 0, st>>>(D, s, E.o_sketch, E.o_s2, vt ? E.o_vt : nullptr, E.o_delta);
+        MUSED_CUDA(cudaGetLastError());
+        mused_count_launches(1);
+    } else {
+        const int ng = D.ell + sl[s].q_len;
+        MUSED_REQUIRE(ng + (ng & 1) <= E.Q.ng_max, "internal: stack of %d rows exceeds scratch %d", ng, E.Q.ng_max);
+        k_bgather<<<std::min(ng, 4 * E.sm_count), 256, 0, st>>>(D, s, E.Q.M);
+        MUSED_CUDA(cudaGetLastError());
+        mused_count_launches(1);
+        if ((rc = merge_query(E.Q, ng, D.d, D.ell, E.sm_count, E.o_sketch, vt ? E.o_vt : nullptr, E.o_s2, st))) return rc;
+        MUSED_CUDA(cudaMemsetAsync(E.o_delta, 0, sizeof(double), st));
+    }
+    if ((rc = b_copy_out(sketch, E.o_sketch, ld_out, where, st))) return rc;
+    if ((rc = b_copy_out(sigma2, E.o_s2, (size_t)D.ell, where, st))) return rc;
+    if ((rc = b_copy_out(vt, E.o_vt, ld_out, where, st))) return rc;
+    if (delta) MUSED_CUDA(cudaMemcpyAsync(delta, E.o_delta, sizeof(double), cudaMemcpyDeviceToHost, st));
+    MUSED_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int bengine_debug(BEngine* Ep, double* scal, double* sigma2, unsigned long long* q_s,
+                  unsigned long long* q_t, long long q_cap) {
+    BEngine& E = *Ep;
+    std::vector<BSlot> sl;
+    int rc = b_read_slots(E, sl);
+    if (rc) return rc;
+    const int capn = E.D.capn, ell = E.D.ell;
+    std::vector<unsigned long long> rs(capn), rt(capn);
+    for (int j = 0; j < E.n_levels; ++j) {
+        for (int side = 0; side < 2; ++side) {
+            const int fd = b_fd_slot(E, j);
+            const int s = side == 0 ? fd : (fd ^ 1);
+            const int o = 2 * j + side;
+            if (scal) {
+                double* r = scal + (size_t)o * 8;
+                r[0] = (double)sl[s].sweeps; r[1] = sl[s].delta; r[2] = 0.0;
+                r[3] = (double)sl[s].last_dump; r[4] = sl[s].q_len;
+                r[5] = (double)sl[s].n_flush; r[6] = (double)sl[s].n_dump; r[7] = (double)sl[s].n_raw;
+            }
+            if (sigma2)
+                MUSED_CUDA(cudaMemcpy(sigma2 + (size_t)o * ell, E.D.s2 + (size_t)s * ell, sizeof(double) * ell, cudaMemcpyDeviceToHost));
+            if (q_s || q_t) {
+                MUSED_REQUIRE(q_cap >= sl[s].q_len, "q_cap too small");
+                MUSED_CUDA(cudaMemcpy(rs.data(), E.D.ringS + (size_t)s * capn, 8 * (size_t)capn, cudaMemcpyDeviceToHost));
+                MUSED_CUDA(cudaMemcpy(rt.data(), E.D.ringT + (size_t)s * capn, 8 * (size_t)capn, cudaMemcpyDeviceToHost));
+                for (int e = 0; e < sl[s].q_len; ++e) {
+                    const int idx = (sl[s].q_head + e) % capn;
+                    if (q_s) q_s[(size_t)o * q_cap + e] = rs[idx];
+                    if (q_t) q_t[(size_t)o * q_cap + e] = rt[idx];
+                }
+            }
+        }
+    }
+    return 0;
+}
+
+int bengine_timing(BEngine* Ep, int enable, double* ms, long long* chunks, long long* rows) {
+    BEngine& E = *Ep;
+    MUSED_CUDA(cudaSetDevice(E.device));
+    for (int k = 0; k < 5; ++k) {
+        for (size_t i = 0; i + 1 < E.ev[k].size(); i += 2) {
+            float t = 0.f;
+            MUSED_CUDA(cudaEventSynchronize(E.ev[k][i + 1]));
+            MUSED_CUDA(cudaEventElapsedTime(&t, E.ev[k][i], E.ev[k][i + 1]));
+            E.timed_ms[k] += t;
+        }
+        for (cudaEvent_t e : E.ev[k]) cudaEventDestroy(e);
+        E.ev[k].clear();
+    }
+    if (ms) for (int k = 0; k < 5; ++k) ms[k] = E.timed_ms[k];
+    if (chunks) *chunks = E.timed_chunks;
+    if (rows) *rows = E.timed_rows;
+    if (enable >= 0) {
+        E.timing = enable != 0;
+        for (int k = 0; k < 5; ++k) E.timed_ms[k] = 0.0;
+        E.timed_chunks = 0;
+        E.timed_rows = 0;
+    }
+    return 0;
+}
+
+}  // namespace mused

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "swfd_device.cuh"
+#include "bswfd.h"
 
 namespace mused {
 
@@ -254,6 +255,43 @@ __global__ void k_fd_out(Dev D, int s, double* sketch, double* sigma2, double* v
     }
 }
 
+
+// Shared tail of both engines' get(): M (ng x d, float64) -> Gram -> Jacobi ->
+// top-l rows shrunk by the (l+1)-th eigenvalue (sliding_windows_frequent_directions.py:160-171).
+int merge_query(const QueryScratch& Q, int ng, long long d, int ell, int sm_count, double* o_sketch,
+                double* o_vt, double* o_s2, cudaStream_t st) {
+    const int nj = ng + (ng & 1);
+    MUSED_REQUIRE(nj <= Q.ng_max, "internal: stack of %d rows exceeds scratch %d", nj, Q.ng_max);
+    MUSED_CUDA(cudaMemsetAsync(Q.G, 0, (size_t)Q.lda * Q.lda * sizeof(double), st));
+    const int tiles = (ng + GT - 1) / GT;
+    k_gram_f64<<<std::min(tiles * tiles, 8 * sm_count), 256, 0, st>>>(Q.M, ng, d, Q.G, Q.lda);
+    MUSED_CUDA(cudaGetLastError());
+    MUSED_CUDA(cudaMemsetAsync(Q.counters, 0, 64 * sizeof(int), st));
+    {
+        int nb = 0;
+        MUSED_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_jacobi, 256, 0));
+        if (nb < 1) nb = 1;
+        if (nb > 4) nb = 4;
+        int grid = nb * sm_count;
+        const long long work = ((long long)nj / 2) * (nj / 2);
+        const int need = (int)std::max(1ll, (work + 255) / 256);
+        if (grid > need) grid = need;
+        double *A_ = Q.G, *V_ = Q.Vq, *cs_ = Q.cs, *scr_ = Q.scr;
+        int n_ = nj, lda_ = Q.lda, sweeps_ = 40;
+        int* cnt_ = Q.counters;
+        void* args[] = {&A_, &V_, &n_, &lda_, &cs_, &sweeps_, &cnt_, &scr_};
+        MUSED_CUDA(cudaLaunchCooperativeKernel((void*)k_jacobi, dim3(grid), dim3(256), args, 0, st));
+    }
+    k_sort_eigs<<<(nj + 255) / 256, 256, 0, st>>>(Q.G, nj, Q.lda, Q.perm, Q.eval);
+    MUSED_CUDA(cudaGetLastError());
+    const int tm = (ell + GT - 1) / GT, tn = (int)((d + GT - 1) / GT);
+    k_merge_out<<<std::min(tm * tn, 8 * sm_count), 256, 0, st>>>(Q.M, ng, d, Q.Vq, Q.lda, Q.perm, Q.eval, ell,
+                                                                  o_sketch, o_vt, o_s2);
+    MUSED_CUDA(cudaGetLastError());
+    COUNT_LAUNCH(4);
+    return 0;
+}
+
 // ---------------------------------------------------------------------------
 // Engine
 // ---------------------------------------------------------------------------
@@ -269,9 +307,7 @@ struct Engine {
     double* stage = nullptr;
     double* norm2 = nullptr;
     // query scratch
-    double *M = nullptr, *G = nullptr, *Vq = nullptr, *cs = nullptr, *eval = nullptr, *scr = nullptr;
-    int *perm = nullptr, *counters = nullptr;
-    int ng_max = 0, lda = 0;
+    QueryScratch Q;
     double *o_sketch = nullptr, *o_vt = nullptr, *o_s2 = nullptr, *o_delta = nullptr;
     int* o_flag = nullptr;
     std::vector<void*> allocs;
@@ -391,18 +427,19 @@ static int engine_create(Engine** out, long long N, long long d, long long ell, 
     A_(E->raw, E->raw_bytes);
     A_(E->stage, (size_t)chunk_rows * d);
     A_(E->norm2, (size_t)chunk_rows);
-    E->ng_max = D.ell + D.capn + 1;
-    E->ng_max += E->ng_max & 1;
-    E->lda = E->ng_max;
+    QueryScratch& Q = E->Q;
+    Q.ng_max = D.ell + D.capn + 1;
+    Q.ng_max += Q.ng_max & 1;
+    Q.lda = Q.ng_max;
     if (!fd_only) {
-        A_(E->M, (size_t)E->ng_max * d);
-        A_(E->G, (size_t)E->lda * E->lda);
-        A_(E->Vq, (size_t)E->lda * E->lda);
-        A_(E->cs, (size_t)E->ng_max);
-        A_(E->eval, (size_t)E->ng_max);
-        A_(E->perm, (size_t)E->ng_max);
-        A_(E->counters, 64);
-        A_(E->scr, 8);
+        A_(Q.M, (size_t)Q.ng_max * d);
+        A_(Q.G, (size_t)Q.lda * Q.lda);
+        A_(Q.Vq, (size_t)Q.lda * Q.lda);
+        A_(Q.cs, (size_t)Q.ng_max);
+        A_(Q.eval, (size_t)Q.ng_max);
+        A_(Q.perm, (size_t)Q.ng_max);
+        A_(Q.counters, 64);
+        A_(Q.scr, 8);
     }
     A_(E->o_sketch, (size_t)ell * d);
     A_(E->o_vt, (size_t)ell * d);
@@ -548,38 +585,11 @@ static int engine_get(Engine& E, int s, bool merge, double* sketch, double* sigm
         COUNT_LAUNCH(1);
     } else {
         const int ng = D.ell + sl.q_len;
-        const int nj = ng + (ng & 1);
-        MUSED_REQUIRE(nj <= E.ng_max, "internal: stack of %d rows exceeds scratch %d", nj, E.ng_max);
-        k_gather_stack<<<std::min(ng, 4 * E.sm_count), 256, 0, st>>>(D, s, E.M);
+        k_gather_stack<<<std::min(ng, 4 * E.sm_count), 256, 0, st>>>(D, s, E.Q.M);
         MUSED_CUDA(cudaGetLastError());
-        MUSED_CUDA(cudaMemsetAsync(E.G, 0, (size_t)E.lda * E.lda * sizeof(double), st));
-        const int tiles = (ng + GT - 1) / GT;
-        k_gram_f64<<<std::min(tiles * tiles, 8 * E.sm_count), 256, 0, st>>>(E.M, ng, D.d, E.G, E.lda);
-        MUSED_CUDA(cudaGetLastError());
-        MUSED_CUDA(cudaMemsetAsync(E.counters, 0, 64 * sizeof(int), st));
-        {
-            int nb = 0;
-            MUSED_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_jacobi, 256, 0));
-            if (nb < 1) nb = 1;
-            if (nb > 4) nb = 4;
-            int grid = nb * E.sm_count;
-            const long long work = ((long long)nj / 2) * (nj / 2);
-            const int need = (int)std::max(1ll, (work + 255) / 256);
-            if (grid > need) grid = need;
-            double *A_ = E.G, *V_ = E.Vq, *cs_ = E.cs, *scr_ = E.scr;
-            int n_ = nj, lda_ = E.lda, sweeps_ = 40;
-            int* cnt_ = E.counters;
-            void* args[] = {&A_, &V_, &n_, &lda_, &cs_, &sweeps_, &cnt_, &scr_};
-            MUSED_CUDA(cudaLaunchCooperativeKernel((void*)k_jacobi, dim3(grid), dim3(256), args, 0, st));
-        }
-        k_sort_eigs<<<(nj + 255) / 256, 256, 0, st>>>(E.G, nj, E.lda, E.perm, E.eval);
-        MUSED_CUDA(cudaGetLastError());
-        const int tm = (D.ell + GT - 1) / GT, tn = (int)((D.d + GT - 1) / GT);
-        k_merge_out<<<std::min(tm * tn, 8 * E.sm_count), 256, 0, st>>>(
-            E.M, ng, D.d, E.Vq, E.lda, E.perm, E.eval, D.ell, E.o_sketch, vt ? E.o_vt : nullptr, E.o_s2);
-        MUSED_CUDA(cudaGetLastError());
+        COUNT_LAUNCH(1);
+        if ((rc = merge_query(E.Q, ng, D.d, D.ell, E.sm_count, E.o_sketch, vt ? E.o_vt : nullptr, E.o_s2, st))) return rc;
         MUSED_CUDA(cudaMemsetAsync(E.o_delta, 0, sizeof(double), st));  // returns 0.0 (:171)
-        COUNT_LAUNCH(5);
     }
     if ((rc = copy_out(sketch, E.o_sketch, ld_out, where, st))) return rc;
     if ((rc = copy_out(sigma2, E.o_s2, (size_t)D.ell, where, st))) return rc;
@@ -593,7 +603,7 @@ static int engine_get(Engine& E, int s, bool merge, double* sketch, double* sigm
 
 using namespace mused;
 
-struct mused_swfd { Engine* E; };
+struct mused_swfd { Engine* E; BEngine* B; };
 struct mused_fd { Engine* E; };
 
 extern "C" {
@@ -612,32 +622,48 @@ int mused_device_count(void) {
 int mused_swfd_create(mused_swfd_t** out, const mused_swfd_cfg* cfg) {
     MUSED_REQUIRE(out && cfg, "NULL argument");
     MUSED_REQUIRE(cfg->n_levels == 0 || cfg->thresholds, "thresholds is NULL");
+    MUSED_REQUIRE(cfg->schedule == MUSED_SCHEDULE_REFERENCE || cfg->schedule == MUSED_SCHEDULE_BATCHED,
+                  "unknown schedule %d", cfg->schedule);
+    if (cfg->schedule == MUSED_SCHEDULE_BATCHED) {
+        BEngine* B = nullptr;
+        int rc = bengine_create(&B, cfg->N, cfg->d, cfg->ell, cfg->beta, cfg->n_levels, cfg->thresholds,
+                                cfg->device, cfg->batch_rows);
+        if (rc) return rc;
+        *out = new mused_swfd{nullptr, B};
+        return 0;
+    }
     Engine* E = nullptr;
     int rc = engine_create(&E, cfg->N, cfg->d, cfg->ell, cfg->beta, cfg->n_levels, cfg->thresholds,
                            cfg->device, cfg->cluster, cfg->chunk_rows, false, 0.0);
     if (rc) return rc;
-    *out = new mused_swfd{E};
+    *out = new mused_swfd{E, nullptr};
     return 0;
 }
 int mused_swfd_destroy(mused_swfd_t* h) {
     if (!h) return 0;
-    cudaSetDevice(h->E->device);
-    delete h->E;
+    if (h->B) {
+        bengine_destroy(h->B);
+    } else {
+        cudaSetDevice(h->E->device);
+        delete h->E;
+    }
     delete h;
     return 0;
 }
 int mused_swfd_fit(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld, int dtype,
                    int where, void* stream) {
     MUSED_REQUIRE(h, "NULL handle");
+    if (h->B) return bengine_fit(h->B, rows, n_rows, ld, dtype, where, (cudaStream_t)stream);
     return engine_feed(*h->E, rows, n_rows, ld, dtype, where, MODE_SEQ, 0, (cudaStream_t)stream);
 }
 int mused_swfd_time(mused_swfd_t* h, uint64_t* t) {
     MUSED_REQUIRE(h && t, "NULL argument");
-    *t = h->E->time;
+    *t = h->B ? bengine_time(h->B) : h->E->time;
     return 0;
 }
 int mused_swfd_profile(mused_swfd_t* h, uint64_t* cycles, int64_t n_inst_cap) {
     MUSED_REQUIRE(h && cycles, "NULL argument");
+    MUSED_REQUIRE(!h->B, "mused_swfd_profile: per-phase cycles exist for schedule=reference only");
     std::vector<Slot> sl;
     Engine& E = *h->E;
     sl.resize(E.D.S);
@@ -652,6 +678,16 @@ int mused_swfd_profile(mused_swfd_t* h, uint64_t* cycles, int64_t n_inst_cap) {
 }
 int mused_swfd_timing(mused_swfd_t* h, int enable, double* ms, int64_t* launches, int64_t* rows) {
     MUSED_REQUIRE(h, "NULL handle");
+    if (h->B) {
+        double k[5];
+        long long c = 0, r = 0;
+        int rc = bengine_timing(h->B, enable, k, &c, &r);
+        if (rc) return rc;
+        if (ms) *ms = k[0] + k[1] + k[2] + k[3] + k[4];
+        if (launches) *launches = c;
+        if (rows) *rows = r;
+        return 0;
+    }
     Engine& E = *h->E;
     MUSED_CUDA(cudaSetDevice(E.device));
     for (size_t i = 0; i + 1 < E.ev.size(); i += 2) {
@@ -674,9 +710,17 @@ int mused_swfd_timing(mused_swfd_t* h, int enable, double* ms, int64_t* launches
     }
     return 0;
 }
+int mused_swfd_kernel_ms(mused_swfd_t* h, int enable, double* ms5, int64_t* chunks, int64_t* rows) {
+    MUSED_REQUIRE(h && h->B, "mused_swfd_kernel_ms needs a schedule=batched handle");
+    long long c = 0, r = 0;
+    int rc = bengine_timing(h->B, enable, ms5, &c, &r);
+    if (chunks) *chunks = c;
+    if (rows) *rows = r;
+    return rc;
+}
 int mused_swfd_queue_capacity(mused_swfd_t* h, int64_t* q) {
     MUSED_REQUIRE(h && q, "NULL argument");
-    *q = h->E->D.capn;
+    *q = h->B ? bengine_qcap(h->B) : h->E->D.capn;
     return 0;
 }
 
@@ -691,6 +735,7 @@ static int read_slots(Engine& E, std::vector<Slot>& sl) {
 int mused_swfd_get(mused_swfd_t* h, double* sketch, double* sigma2, double* vt, double* delta,
                    int32_t* level, int where, void* stream) {
     MUSED_REQUIRE(h && sketch && sigma2, "NULL argument");
+    if (h->B) return bengine_get(h->B, sketch, sigma2, vt, delta, level, where, (cudaStream_t)stream);
     Engine& E = *h->E;
     if (E.n_levels == 0) {  // the reference raises KeyError: 0 here
         set_error("SeqBasedSWFD has zero levels (R <= 1): get() is undefined");
@@ -721,6 +766,7 @@ int mused_swfd_get(mused_swfd_t* h, double* sketch, double* sigma2, double* vt, 
 
 int mused_swfd_size(mused_swfd_t* h, int64_t* n) {
     MUSED_REQUIRE(h && n, "NULL argument");
+    if (h->B) { long long v = 0; int rc = bengine_size(h->B, &v); *n = v; return rc; }
     std::vector<Slot> sl;
     int rc = read_slots(*h->E, sl);
     if (rc) return rc;
@@ -734,6 +780,7 @@ int mused_swfd_size(mused_swfd_t* h, int64_t* n) {
 int mused_swfd_debug(mused_swfd_t* h, double* scal, double* sigma2, uint64_t* q_s, uint64_t* q_t,
                      int64_t q_cap) {
     MUSED_REQUIRE(h, "NULL handle");
+    if (h->B) return bengine_debug(h->B, scal, sigma2, (unsigned long long*)q_s, (unsigned long long*)q_t, q_cap);
     Engine& E = *h->E;
     std::vector<Slot> sl;
     int rc = read_slots(E, sl);

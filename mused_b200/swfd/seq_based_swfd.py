@@ -16,14 +16,21 @@ from .. import _lib
 
 class SeqBasedSWFD:
     def __init__(self, N: int, R: float, d: int, sketch_dim: int, beta: float = 1.0, *,
-                 device: int = 0, cluster: int = 0, chunk_rows: int = 0, **kwargs):
+                 device: int = 0, cluster: int = 0, chunk_rows: int = 0,
+                 schedule: str = "reference", batch_rows: int = 0, **kwargs):
         """Sliding Window on Frequent Directions (seq_based_swfd.py:12-44).
 
         Args (reference): N window size, R upper bound of squared row norm,
         d row dimension, sketch_dim, beta; kwarg ``upper_F_norm`` switches the
         level count to ceil(log2(F/N)) (:31-37).
         Extras (keyword-only): device ordinal, cluster (CTAs per FD instance,
-        0 = auto), chunk_rows (rows staged per launch).
+        0 = auto), chunk_rows (rows staged per launch), schedule:
+          "reference"  every flush / dump decision of the reference, row by row
+                       (float64, bit-faithful schedule; the parity path);
+          "batched"    one tensor-core Gram + eigensolve + rotate per chunk of
+                       batch_rows (default sketch_dim) rows, all directions with
+                       sigma^2 >= threshold dumped per chunk (the throughput path;
+                       semantics stated in oracle/swfd_batched_oracle.py).
         """
         self.N = np.uint64(N)
         self.d = int(d)
@@ -41,8 +48,12 @@ class SeqBasedSWFD:
         self.thresholds = thr
         lib = _lib.load()
         arr = (C.c_double * max(1, len(thr)))(*thr)
+        if schedule not in _lib.SCHEDULES:
+            raise ValueError("schedule must be 'reference' or 'batched', got %r" % (schedule,))
+        self.schedule = schedule
         cfg = _lib.SwfdCfg(int(N), self.d, self.sketch_dim, float(beta), len(thr), arr,
-                           int(device), int(cluster), int(chunk_rows))
+                           int(device), int(cluster), int(chunk_rows),
+                           _lib.SCHEDULES[schedule], int(batch_rows))
         self._h = C.c_void_p()
         _lib.check(lib.mused_swfd_create(C.byref(self._h), C.byref(cfg)))
         self._lib = lib
@@ -124,6 +135,15 @@ class SeqBasedSWFD:
         ms, nl, nr = C.c_double(0.0), C.c_int64(0), C.c_int64(0)
         _lib.check(self._lib.mused_swfd_timing(self._h, int(enable), C.byref(ms), C.byref(nl), C.byref(nr)))
         return float(ms.value), int(nl.value), int(nr.value)
+
+    KERNELS = ("K1_stage", "K5_book", "K2_gram", "K3_eig", "K4_rotate")
+
+    def kernel_ms(self, enable=-1):
+        """schedule="batched": ({kernel class: ms}, chunks, rows) since timing was armed."""
+        ms = (C.c_double * 5)()
+        nc, nr = C.c_int64(0), C.c_int64(0)
+        _lib.check(self._lib.mused_swfd_kernel_ms(self._h, int(enable), ms, C.byref(nc), C.byref(nr)))
+        return dict(zip(self.KERNELS, (float(v) for v in ms))), int(nc.value), int(nr.value)
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h.value:
