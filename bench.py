@@ -46,6 +46,10 @@ def parse():
     ap.add_argument("--cpu-rows", type=int, default=0, help="rows of the cpu_baseline sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--schedule", default="batched", choices=["batched", "reference"],
+                    help="batched: north_star's chunked tensor-core schedule (headline); "
+                         "reference: the reference's per-row flush schedule")
+    ap.add_argument("--no-refsched", action="store_true", help="skip the extra reference-schedule timing")
     return ap.parse_args()
 
 
@@ -56,6 +60,14 @@ def measured_peaks():
             j = json.load(f)
         return float(j["hbm_gbs"]), "measured"
     return 6650.0, "fallback"
+
+
+def measured_tensor_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["bf16_tflops"])
+    return 1590.0
 
 
 def make_stream(n_rows, seed):
@@ -72,47 +84,62 @@ def centroids(seed):
 
 
 class ClockSampler:
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
-         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock + throttle reasons DURING the timed region (the profiling recipe's
+    clocks line), read through NVML in-process every 250 ms: a polling nvidia-smi
+    child process slowed this launch-heavy step by ~40 % (it serialises with kernel
+    launches in the driver), NVML queries from a thread do not."""
 
     def __init__(self, index):
         self.index = index
-        self.lines = []
-        self.proc = None
+        self.sm, self.mx, self.reasons = [], [], set()
+        self.stop_flag = threading.Event()
+        self.thread = None
+        self.err = None
+
+    def _run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = self.index
+            if vis:
+                try:
+                    idx = int(vis.split(",")[self.index])
+                except Exception:
+                    idx = self.index
+            h = nv.nvmlDeviceGetHandleByIndex(idx)
+            mx = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            names = {"hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+                     "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                     "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+                     "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4)}
+            while not self.stop_flag.is_set():
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                self.mx.append(mx)
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    for k, bit in names.items():
+                        if r & bit:
+                            self.reasons.add(k)
+                except Exception:
+                    pass
+                self.stop_flag.wait(0.25)
+        except Exception as e:                      # pragma: no cover
+            self.err = repr(e)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200"],
-                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
-        except Exception:
-            self.proc = None
-
-    def _read(self):
-        for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        sm, mx, reasons = [], [], set()
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 9:
-                continue
-            try:
-                sm.append(float(f[1]))
-                mx.append(float(f[2]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        if self.thread is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["not sampled"]}
+        self.stop_flag.set()
+        self.thread.join(timeout=2.0)
+        if not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: %s" % self.err]}
+        return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": max(self.mx), "reasons": sorted(self.reasons),
+                "samples": len(self.sm), "source": "nvml"}
 
 
 # ---------------------------------------------------------------------------
@@ -223,50 +250,62 @@ def run_ours(args, rank, local_rank, world):
             return float(t.item())
         return x
 
-    # ---------------- device-resident arm (`value`) -------------------------
     Ad = torch.as_tensor(A).to(dev)                        # inputs resident in HBM before timing
-    sk = SeqBasedSWFD(WIN, R, D, ELL, device=local_rank, cluster=args.cluster)
-    labels_keep = None
-
-    def step_dev(i):
-        blk = Ad[i * WIN:(i + 1) * WIN]
-        sk.fit(blk)
-        out = sk.get()
-        lab = mo.cosine_assign(blk, Cd, TAU, device=dev)
-        return out, lab
-
-    for i in range(args.warmup):
-        step_dev(i)
-    barrier()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
-    sk.kernel_timing(enable=1)
-    l0 = lib.mused_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(args.warmup, n_steps):
-        out, labels_keep = step_dev(i)
-    e1.record()
-    barrier()
-    ms_total = max_over_ranks(e0.elapsed_time(e1))
-    launches = int(lib.mused_launch_count() - l0)
-    k_ms, k_launches, k_rows = sk.kernel_timing(enable=0)
-    clocks = sampler.stop() if rank == 0 else None
-    value = world * args.steps * WIN / (ms_total * 1e-3)
-    st = sk.debug_state()
-    n_inst = len(st)
-    prof = sk.profile()
-    last_level = sk.last_level
-    sk.close()
-    del Ad
+
+    def device_arm(schedule, warmup, steps, sample_clocks):
+        """`value`: whole windows (fit + get + assign) with inputs resident in HBM."""
+        sk = SeqBasedSWFD(WIN, R, D, ELL, device=local_rank, cluster=args.cluster, schedule=schedule)
+
+        def step(i):
+            blk = Ad[i * WIN:(i + 1) * WIN]
+            sk.fit(blk)
+            out = sk.get()
+            lab = mo.cosine_assign(blk, Cd, TAU, device=dev)
+            return out, lab
+
+        for i in range(warmup):
+            step(i)
+        barrier()
+        sampler = ClockSampler(local_rank)
+        if sample_clocks and rank == 0:
+            sampler.start()
+        if schedule == "batched":
+            sk.kernel_ms(enable=1)
+        else:
+            sk.kernel_timing(enable=1)
+        l0 = lib.mused_launch_count()
+        e0.record()
+        for i in range(warmup, warmup + steps):
+            out, lab = step(i)
+        e1.record()
+        barrier()
+        ms_total = max_over_ranks(e0.elapsed_time(e1))
+        res = {"ms_total": ms_total, "launches": int(lib.mused_launch_count() - l0),
+               "value": world * steps * WIN / (ms_total * 1e-3), "sketch": out[0],
+               "clocks": sampler.stop() if (sample_clocks and rank == 0) else None}
+        if schedule == "batched":
+            res["kernel_ms"], res["chunks"], res["k_rows"] = sk.kernel_ms(enable=0)
+        else:
+            res["k_ms"], res["k_launches"], res["k_rows"] = sk.kernel_timing(enable=0)
+            res["prof"] = sk.profile()
+        res["state"] = sk.debug_state()
+        res["level"] = sk.last_level
+        sk.close()
+        return res
+
+    main_res = device_arm(args.schedule, args.warmup, args.steps, True)
+    other = None
+    if args.schedule == "batched" and not args.no_refsched:
+        # the bit-faithful reference flush schedule on the same stream (1 warm-up + 2 timed windows)
+        other = device_arm("reference", 1, min(2, args.steps), False)
 
     # ---------------- end-to-end arm (`e2e`): host buffers through the public API
     e2e = None
     if not args.no_e2e:
         Ah = torch.as_tensor(A).pin_memory()
         An = Ah.numpy()
-        sk2 = SeqBasedSWFD(WIN, R, D, ELL, device=local_rank, cluster=args.cluster)
+        sk2 = SeqBasedSWFD(WIN, R, D, ELL, device=local_rank, cluster=args.cluster, schedule=args.schedule)
         lab_host = torch.empty(WIN, dtype=torch.int32).pin_memory()
 
         def step_e2e(i):
@@ -294,26 +333,68 @@ def run_ours(args, rank, local_rank, world):
                "d2h_bytes_per_step": 2 * ELL * D * 8 + ELL * 8 + 8 + WIN * 4,
                "wall_s": time.perf_counter() - t0}
         sk2.close()
+    del Ad
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    # ---------------- roofline of the dominant kernel ------------------------
-    S = n_inst
+    # ---------------- roofline of the dominant kernel + per-kernel figures ----------
+    S = len(main_res["state"])
     bytes_per_row = 8 * D + S * 20 * D                     # append 8d + S*20d per row
     peak, how = measured_peaks()
-    roofline = None
-    if k_launches:
-        rows_per_launch = k_rows / k_launches
-        dur_s = (k_ms / k_launches) * 1e-3
+    tpeak = measured_tensor_peak()
+    roofline, kernels = None, None
+    if args.schedule == "batched":
+        km, chunks = main_res["kernel_ms"], max(1, main_res["chunks"])
+        rows_per_launch = main_res["k_rows"] / chunks
+        dom = max(km, key=km.get)
+        dur_s = km[dom] / chunks * 1e-3
+        achieved = bytes_per_row * rows_per_launch / dur_s / 1e9
+        roofline = {"bound": "hbm", "kernel": {"K1_stage": "k_bstage", "K5_book": "k_bbook", "K2_gram": "k_gram_tc",
+                                                "K3_eig": "k_eig_jacobi", "K4_rotate": "k_brotate"}[dom],
+                    "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                    "peak_source": how, "algorithmic_bytes_per_row": bytes_per_row,
+                    "rows_per_launch": rows_per_launch, "avg_launch_ms": km[dom] / chunks,
+                    "share_of_step": km[dom] / main_res["ms_total"],
+                    "note": "dominant kernel is the batched float64 eigensolve (FP64-issue / cluster-barrier bound, "
+                            "no HBM or tensor roofline applies); bytes are SURVEY 8(d)'s per-row figure"}
+        n2 = 2 * ELL
+        us = {k: v / chunks * 1e3 for k, v in km.items()}
+        kernels = {
+            "K1_stage": {"us_per_chunk": us["K1_stage"], "bound": "hbm",
+                         "achieved_GBs": rows_per_launch * D * 12 / (us["K1_stage"] * 1e-6) / 1e9,
+                         "algorithmic_bytes": "rows*d*(4 read + 8 hi/lo write)"},
+            "K2_gram": {"us_per_chunk": us["K2_gram"], "bound": "tensor",
+                        "achieved_TFLOPs_dense": S * 2.0 * n2 * n2 * D / (us["K2_gram"] * 1e-6) / 1e12,
+                        "issued_TFLOPs_3xTF32": 3 * S * 2.0 * n2 * n2 * D / (us["K2_gram"] * 1e-6) / 1e12,
+                        "peak_bf16_TFLOPs": tpeak, "note": "kind::tf32 runs at half the bf16 rate; 3 passes"},
+            "K3_eig": {"us_per_chunk": us["K3_eig"], "bound": "fp64-issue/barrier",
+                       "share_of_step": km["K3_eig"] / main_res["ms_total"]},
+            "K4_rotate": {"us_per_chunk": us["K4_rotate"], "bound": "fp32 SIMT",
+                          "achieved_TFLOPs": S * 2.0 * ELL * n2 * D / (us["K4_rotate"] * 1e-6) / 1e12},
+            "K5_book": {"us_per_chunk": us["K5_book"]},
+        }
+    elif main_res.get("k_launches"):
+        rows_per_launch = main_res["k_rows"] / main_res["k_launches"]
+        dur_s = (main_res["k_ms"] / main_res["k_launches"]) * 1e-3
         achieved = bytes_per_row * rows_per_launch / dur_s / 1e9
         roofline = {"bound": "hbm", "kernel": "k_swfd_rows", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "traffic": None, "peak_source": how,
                     "algorithmic_bytes_per_row": bytes_per_row, "rows_per_launch": rows_per_launch,
-                    "avg_launch_ms": k_ms / k_launches, "share_of_step": k_ms / ms_total,
+                    "avg_launch_ms": main_res["k_ms"] / main_res["k_launches"],
+                    "share_of_step": main_res["k_ms"] / main_res["ms_total"],
                     "note": "reference flush schedule is a per-row dependency chain (latency/FP64-bound), see DESIGN.md"}
+
+    # covariance error of the last timed window, both schedules, against the exact window
+    from oracle import swfd_oracle as so
+    Aw = A[(n_steps - 1) * WIN:n_steps * WIN].astype(np.float64)
+    cov = {args.schedule: so.cov_error(Aw, main_res["sketch"]), "bound_1_over_l": 1.0 / ELL}
+    if other is not None:
+        lastw = 1 + min(2, args.steps)
+        cov["reference_schedule_window"] = so.cov_error(A[(lastw - 1) * WIN:lastw * WIN].astype(np.float64),
+                                                        other["sketch"])
 
     cpu = None
     if not args.no_cpu:
@@ -323,24 +404,35 @@ def run_ours(args, rank, local_rank, world):
                "sample": "rows 256..%d of the same stream (after 256 untimed warm-up rows) + one get() + assign, %.1fs"
                          % (256 + rows, dt)}
 
-    ph_tot = {}
-    for p in prof:
-        for k, v in p.items():
-            ph_tot[k] = ph_tot.get(k, 0) + v
+    st = main_res["state"]
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "metric": METRIC, "value": main_res["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": main_res["ms_total"] / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32 rows, 3xTF32 products, f64 eigensolve"
+        if args.schedule == "batched" else "f64", "data": "synthetic",
         "config": {"workload": "SWFD d=1024 l=128 N=10000 low-rank+noise stream + cosine assign k=150 (configs[1])",
-                   "schedule": "reference", "levels": S // 2, "fd_instances": S, "rows_per_step": WIN,
-                   "l2": "each step streams a fresh 41 MB window; FD state (~%.0f MB) is meant to stay L2-resident"
-                         % (S * (2 * 2 * ELL * D * 8 + 3 * (2 * ELL + 2) ** 2 * 8) / 1e6),
-                   "query_level": last_level},
-        "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
+                   "schedule": args.schedule, "levels": S // 2, "fd_instances": S, "rows_per_step": WIN,
+                   "l2": "each step streams a fresh 41 MB window (> nothing cached from the previous step's rows); "
+                         "FD state is meant to stay L2-resident",
+                   "query_level": main_res["level"]},
+        "clocks": main_res["clocks"], "e2e": e2e, "gpu_launches": main_res["launches"], "roofline": roofline,
+        "cpu_baseline": cpu, "cov_error": cov,
         "flushes_per_row": sum(o["n_flush"] for o in st) / float(n_steps * WIN),
-        "phase_cycles_share": {k: v / max(1, sum(x for kk, x in ph_tot.items() if kk != "rows"))
-                               for k, v in ph_tot.items() if k != "rows"},
     }
+    if kernels:
+        line["kernels"] = kernels
+    if other is not None:
+        line["reference_schedule"] = {"value": other["value"], "unit": UNIT, "dtype": "f64",
+                                      "ms_per_step": other["ms_total"] / min(2, args.steps),
+                                      "note": "bit-faithful flush/dump schedule of the reference on the same stream "
+                                              "(strict parity path, tests/test_swfd_gpu.py)"}
+    if args.schedule == "reference":
+        ph_tot = {}
+        for p in main_res["prof"]:
+            for k, v in p.items():
+                ph_tot[k] = ph_tot.get(k, 0) + v
+        line["phase_cycles_share"] = {k: v / max(1, sum(x for kk, x in ph_tot.items() if kk != "rows"))
+                                      for k, v in ph_tot.items() if k != "rows"}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

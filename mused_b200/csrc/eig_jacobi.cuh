@@ -66,6 +66,14 @@ struct EigSmem {
     double cut;
 };
 
+// One Hestenes rotation of the column pair (x, y) with squared norms (nx, ny);
+// afterwards the two columns have traded places (odd-even transposition
+// ordering), which is folded into the rotation so no register moves are spent.
+// FP64 issue is the bottleneck of this kernel (64 DFMA/clk/SM), so the rotation
+// ANGLE is taken in fp32 (MUFU rsqrt / sqrt, tangent good to ~1e-7) while the
+// pair (c, s) is refined to float64 (two Newton steps on rsqrt) so that
+// c^2 + s^2 = 1 to 1e-16 and W stays G times an orthogonal matrix.  The norms
+// follow the rotation that was actually applied.
 template <int EPL>
 __device__ __forceinline__ void jacobi_pair(double (&x)[EPL], double (&y)[EPL], double& nx, double& ny,
                                             double nmax, double& off) {
@@ -73,35 +81,38 @@ __device__ __forceinline__ void jacobi_pair(double (&x)[EPL], double (&y)[EPL], 
 #pragma unroll
     for (int e = 0; e < EPL; ++e) g = fma(x[e], y[e], g);
     g = warp_sum(g);
-    const double prod = nx * ny;
-    if (g != 0.0 && prod > 0.0) {
-        const double rel = fabs(g) * rsqrt(prod);
-        if (prod > 1e-24 * nmax * nmax) off = fmax(off, rel);
-        if (rel > 1e-15) {
-            const double zeta = (ny - nx) / (2.0 * g);
-            const double t = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-            const double c = rsqrt(1.0 + t * t);
-            const double s = c * t;
-#pragma unroll
-            for (int e = 0; e < EPL; ++e) {
-                const double xv = x[e], yv = y[e];
-                x[e] = c * xv - s * yv;
-                y[e] = s * xv + c * yv;
-            }
-            nx -= t * g;
-            ny += t * g;
-        }
+    const float gf = (float)g, nxf = (float)nx, nyf = (float)ny;
+    float relf = 0.f;
+    if (nxf > 0.f && nyf > 0.f) relf = fabsf(gf) * rsqrtf(nxf) * rsqrtf(nyf);
+    if (nx * ny > 1e-24 * nmax * nmax) off = fmax(off, (double)relf);
+    double c = 0.0, s = 1.0;            // pure swap: x_new = y, y_new = x
+    double mx = ny, my = nx;
+    if (relf > 1e-10f) {
+        const float zf = (float)(ny - nx) / (2.f * gf);
+        const float tf = copysignf(1.f, zf) / (fabsf(zf) + sqrtf(fmaf(zf, zf, 1.f)));
+        const double t = (double)tf;
+        const double u = fma(t, t, 1.0);
+        double c0 = (double)rsqrtf((float)u);
+        c0 = c0 * fma(-0.5 * u, c0 * c0, 1.5);
+        c0 = c0 * fma(-0.5 * u, c0 * c0, 1.5);
+        const double s0 = c0 * t;
+        // rotated pair (c0 x - s0 y, s0 x + c0 y), stored swapped
+        c = s0;
+        s = c0;
+        const double cc = c0 * c0, ss = s0 * s0, cs2 = 2.0 * c0 * s0 * g;
+        mx = fma(ss, nx, fma(cc, ny, cs2));      // |s0 x + c0 y|^2
+        my = fma(cc, nx, fma(ss, ny, -cs2));     // |c0 x - s0 y|^2
     }
-    // the pair trades places (odd-even transposition ordering)
+    // x_new = c x + s y,  y_new = s x - c y   (swap: c = 0, s = 1 gives x_new = y, y_new = x)
+    const bool rotated = relf > 1e-10f;
 #pragma unroll
     for (int e = 0; e < EPL; ++e) {
-        const double tmp = x[e];
-        x[e] = y[e];
-        y[e] = tmp;
+        const double xv = x[e], yv = y[e];
+        x[e] = fma(c, xv, s * yv);
+        y[e] = rotated ? fma(s, xv, -c * yv) : xv;
     }
-    const double tn = nx;
-    nx = ny;
-    ny = tn;
+    nx = mx;
+    ny = my;
 }
 
 // Grid = S * EPL CTAs, cluster = EPL CTAs, EIG_NT threads, dynamic smem = sizeof(EigSmem<EPL>).

@@ -1,0 +1,138 @@
+"""GPU parity of the batched-schedule engine (schedule="batched": tcgen05 3xTF32
+Gram, cluster Jacobi eigensolve, rotate, snapshot bookkeeping) through the C ABI
+against its float64 statement oracle/swfd_batched_oracle.py on the same seeded
+streams.
+
+Bars: identical schedule (snapshot (s, t) stamps, flush / dump / raw counts, chosen
+level, get_size); singular values within 1e-4 relative for sigma >= 0.05 sigma_max
+and 1e-5 sigma_max absolute below (the Gram route carries fp32 products: an
+eigenvalue is known to ~1e-6 lambda_max absolute, so sigma_i to 5e-7 (sigma_max /
+sigma_i)^2 relative); covariance error within 1e-3 relative (north_star) -- the
+asserted bounds are 20x tighter than north_star's."""
+import numpy as np
+import pytest
+import torch
+
+from mused_b200 import synth
+from oracle import swfd_oracle as so
+from oracle.swfd_batched_oracle import BatchedSeqSWFD
+
+pytestmark = pytest.mark.gpu
+
+SIG_RTOL = 5e-6      # north_star: 1e-4
+COV_RTOL = 5e-5      # north_star: 1e-3
+
+
+def _check_query(gpu, ora, Aw):
+    sg, s2g, vtg, dg = gpu.get()
+    so_, s2o, _, do = ora.get()
+    assert gpu.last_level == ora.pick_level()
+    a, b = np.sqrt(np.maximum(s2o, 0)), np.sqrt(np.maximum(s2g, 0))
+    big = a >= 0.05 * a.max()
+    assert np.max(np.abs(a[big] - b[big]) / a[big]) <= SIG_RTOL
+    assert np.max(np.abs(a[~big] - b[~big]), initial=0.0) <= 1e-5 * a.max()
+    eg, eo = so.cov_error(Aw, sg), so.cov_error(Aw, so_)
+    assert abs(eg - eo) <= COV_RTOL * eo, (eg, eo)
+    assert eg <= 4.0 / gpu.sketch_dim                      # DS-FD bound (test_bibd.py:80-81)
+    assert gpu.get_size() == ora.get_size()
+    nz = s2g > 1e-9 * s2g.max()
+    np.testing.assert_allclose(np.linalg.norm(vtg[nz], axis=1), 1.0, atol=1e-5)
+    for g, o in zip(gpu.debug_state(), ora.debug_state()):
+        assert g["q_s"] == o["q_s"] and g["q_t"] == o["q_t"]
+        assert (g["n_flush"], g["n_dump"], g["n_raw"]) == (o["n_flush"], o["n_dump"], o["n_raw"])
+        assert g["last_dump_time"] == o["last_dump_time"]
+        assert abs(g["delta"] - o["delta"]) <= 1e-5 * o["delta"] + 1e-12
+        np.testing.assert_allclose(np.sort(g["s2"]), np.sort(o["s2"]), atol=2e-5 * max(o["s2"].max(), 1e-30))
+    return eg, eo
+
+
+@pytest.mark.parametrize("ell,d,N,n,scale", [
+    (16, 128, 500, 2000, 1.0),
+    (16, 128, 500, 1500, 3.0),
+    (32, 256, 700, 2100, 2.0),
+    (64, 512, 1000, 2500, 2.0),        # BASELINE configs[0] shape (d=512, l=64), shortened
+    (128, 1024, 2000, 4000, 2.0),      # BASELINE configs[1] shape (d=1024, l=128), shortened
+])
+def test_batched_engine_matches_batched_oracle(ell, d, N, n, scale):
+    from mused_b200.swfd import SeqBasedSWFD
+    A = synth.lowrank_stream(n, d, seed=3, scale=scale)
+    A64 = A.astype(np.float64)
+    R = synth.row_norm2_max(A)
+    gpu = SeqBasedSWFD(N, R, d, ell, schedule="batched")
+    ora = BatchedSeqSWFD(N, R, d, ell)
+    q = N // 2
+    for t in range(0, n, q):
+        gpu.fit(A[t:t + q])
+        ora.fit(A64[t:t + q])
+        te = min(t + q, n)
+        if te >= N:
+            _check_query(gpu, ora, A64[te - N:te])
+    gpu.close()
+
+
+def test_batched_engine_is_independent_of_call_slicing():
+    """fit() of single rows, ragged blocks and one big block give the same state
+    (chunk boundaries depend on the stream position and on get() only); device
+    tensors, float64 and int64 inputs are accepted."""
+    from mused_b200.swfd import SeqBasedSWFD
+    rng = np.random.default_rng(5)
+    ell, d, N, n = 16, 96, 300, 700
+    A = (rng.standard_normal((n, d)) * np.exp(0.5 * rng.standard_normal(n))[:, None]).astype(np.float32)
+    R = synth.row_norm2_max(A)
+    outs = []
+    for mode in ("rows", "ragged", "block_cuda_f64"):
+        sk = SeqBasedSWFD(N, R, d, ell, schedule="batched")
+        if mode == "rows":
+            for r in range(n):
+                sk.fit(A[r:r + 1])
+        elif mode == "ragged":
+            pos = 0
+            for step in (1, 7, 33, 100, 250, 309):
+                sk.fit(A[pos:pos + step])
+                pos += step
+            assert pos == n
+        else:
+            sk.fit(torch.as_tensor(A).cuda().double())
+        assert int(sk.time) == n
+        outs.append((sk.get(), sk.debug_state(), sk.get_size()))
+        sk.close()
+    (s0, st0, z0) = outs[0]
+    for (s1, st1, z1) in outs[1:]:
+        assert z0 == z1
+        np.testing.assert_array_equal(s0[1], s1[1])
+        np.testing.assert_array_equal(np.abs(s0[0]), np.abs(s1[0]))
+        for a, b in zip(st0, st1):
+            assert a["q_t"] == b["q_t"] and a["q_s"] == b["q_s"]
+
+
+def test_batched_engine_adjacency_rows_and_cov_error_vs_reference_schedule():
+    """0/1 int64 rows like main.py feeds (matrix_operations.py:138); the batched
+    schedule's covariance error stays within 25% of the reference schedule's
+    (oracle port of the reference) and under the DS-FD bound."""
+    from mused_b200.swfd import SeqBasedSWFD
+    rng = np.random.default_rng(9)
+    W, ell = 256, 16
+    X = (rng.random((3 * W, W)) < 0.08).astype(np.int64)
+    R = float((X * X).sum(1).max())
+    gpu = SeqBasedSWFD(N=W, R=R, d=W, sketch_dim=ell, schedule="batched")
+    ref = so.SeqSWFD(W, R, W, ell)
+    X64 = X.astype(np.float64)
+    for t in range(3 * W):
+        ref.fit(X64[t:t + 1])
+    gpu.fit(X)
+    Aw = X64[-W:]
+    eg = so.cov_error(Aw, gpu.get()[0])
+    er = so.cov_error(Aw, ref.get()[0])
+    assert eg <= 4.0 / ell and er <= 4.0 / ell
+    assert eg <= 1.25 * er + 1e-3, (eg, er)
+    gpu.close()
+
+
+def test_batched_engine_rejects_unsupported_shapes():
+    from mused_b200.swfd import SeqBasedSWFD
+    with pytest.raises(ValueError):
+        SeqBasedSWFD(100, 8.0, 128, 24, schedule="batched")     # sketch_dim not in {16,32,64,128}
+    with pytest.raises(ValueError):
+        SeqBasedSWFD(100, 8.0, 100, 16, schedule="batched")     # d % 32 != 0
+    with pytest.raises(ValueError):
+        SeqBasedSWFD(100, 8.0, 128, 16, schedule="nope")
