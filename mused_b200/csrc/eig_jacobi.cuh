@@ -24,8 +24,9 @@
 namespace mused {
 namespace cg = cooperative_groups;
 
-constexpr int EIG_WARPS = 16;               // warps per CTA
+constexpr int EIG_WARPS = 4;                // warps per CTA (one per SM sub-partition)
 constexpr int EIG_NT = EIG_WARPS * 32;
+constexpr int EIG_C = 4;                    // columns per block; a warp owns two blocks
 
 struct BSlot {                               // one FD instance of the batched engine
     double delta, error;
@@ -56,63 +57,201 @@ struct EigArgs {
 template <int EPL>
 struct EigSmem {
     static constexpr int N2 = 32 * EPL;
-    double slotA[EIG_WARPS][N2];
-    double slotB[EIG_WARPS][N2];
-    double lam[N2];           // eigenvalue per position (replicated in every CTA)
-    double red_off[8 * EIG_WARPS];   // per (cta, warp) partial maxima, written into CTA 0
-    double red_nmax[8 * EIG_WARPS];
-    double normA[EIG_WARPS];         // squared norms travelling with slotA / slotB
-    double normB[EIG_WARPS];
+    double slotA[EIG_WARPS][EIG_C][N2];   // first blocks on their way to the left neighbour
+    double slotB[EIG_WARPS][EIG_C][N2];   // rotated blocks on their way to the right neighbour
+    double normA[EIG_WARPS][EIG_C];
+    double normB[EIG_WARPS][EIG_C];
+    double lam[N2];                       // eigenvalue per column id (replicated in every CTA)
+    double red_off[64];                   // per-warp partial maxima, collected in CTA 0
+    double red_nmax[64];
     double cut;
 };
 
-// One Hestenes rotation of the column pair (x, y) with squared norms (nx, ny);
-// afterwards the two columns have traded places (odd-even transposition
-// ordering), which is folded into the rotation so no register moves are spent.
-// FP64 issue is the bottleneck of this kernel (64 DFMA/clk/SM), so the rotation
-// ANGLE is taken in fp32 (MUFU rsqrt / sqrt, tangent good to ~1e-7) while the
-// pair (c, s) is refined to float64 (two Newton steps on rsqrt) so that
-// c^2 + s^2 = 1 to 1e-16 and W stays G times an orthogonal matrix.  The norms
-// follow the rotation that was actually applied.
-template <int EPL>
-__device__ __forceinline__ void jacobi_pair(double (&x)[EPL], double (&y)[EPL], double& nx, double& ny,
-                                            double nmax, double& off) {
-    double g = 0.0;
+// ---- distributed shared memory by cluster address -----------------------------------------
+__device__ __forceinline__ uint32_t dsmem_addr(const void* p, int rank) {
+    uint32_t a = (uint32_t)__cvta_generic_to_shared(p), r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ double dsmem_ld(uint32_t addr) {
+    double v;
+    asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void dsmem_st(uint32_t addr, double v) {
+    asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
+__device__ __forceinline__ void cluster_barrier() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ double rsqrt_approx(double x) {       // MUFU.RSQ64H: ~20 bits
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    return y;
+}
+__device__ __forceinline__ double rcp_approx(double x) {         // MUFU.RCP64H: ~20 bits
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    return y;
+}
+__device__ __forceinline__ double sel(bool p, double a, double b) { return p ? a : b; }
+
+// Hestenes rotation of a column pair with inner product g and squared norms
+// (nx, ny): branch-free, float64 pipe only (no fp32 detour: F2F conversions and
+// IEEE fp32 division cost more issue slots than they save).  The TANGENT comes
+// from 20-bit MUFU seeds (t = b sgn(a) / (|a| + sqrt(a^2 + b^2)), a = ny - nx,
+// b = 2g), which is all the convergence needs; (c, s) is then refined so that
+// c^2 + s^2 = 1 to 1e-16 (two Newton steps on rsqrt(1 + t^2)), i.e. W stays G
+// times an orthogonal matrix.  Norms follow the rotation actually applied.
+__device__ __forceinline__ void jacobi_angle(double g, double nx, double ny, double nmax, double& off,
+                                             double& c, double& s, double& mx, double& my) {
+    const double prod = nx * ny;
+    const double rel = fabs(g) * rsqrt_approx(prod);
+    const bool live = prod > 0.0;
+    if (live && prod > 1e-24 * nmax * nmax) off = fmax(off, rel);
+    const bool apply = live && rel > 1e-10;
+    const double a = ny - nx, b = g + g;
+    const double q2 = fma(a, a, b * b);
+    const double r = q2 * rsqrt_approx(q2);
+    const double tb = b * rcp_approx(fabs(a) + r);
+    const double t = sel(a < 0.0, -tb, tb);
+    const double u = fma(t, t, 1.0);
+    double c0 = rsqrt_approx(u);
+    c0 = c0 * fma(-0.5 * u, c0 * c0, 1.5);
+    c0 = c0 * fma(-0.5 * u, c0 * c0, 1.5);
+    c = sel(apply, c0, 1.0);
+    s = sel(apply, c0 * t, 0.0);
+    const double cc = c * c, ss = s * s, cs2 = (c + c) * s * g;
+    mx = fma(cc, nx, fma(ss, ny, -cs2));     // |c x - s y|^2
+    my = fma(ss, nx, fma(cc, ny, cs2));      // |s x + c y|^2
+}
+
+// Four independent rotations (column ids A_k, B_k of the warp's eight columns).
+// The four inner products are reduced together (6 shuffles instead of 20: after
+// the xor-16 and xor-8 steps lane group q = lane/8 owns product q), group q
+// computes the angle of rotation q, and (c, s, new norms) are broadcast back.
+template <int EPL, int A0, int B0, int A1, int B1, int A2, int B2, int A3, int B3>
+__device__ __forceinline__ void rot4(double (&col)[8][EPL], double (&nrm)[8], double nmax, double& off,
+                                     int lane) {
+    constexpr int IA[4] = {A0, A1, A2, A3};
+    constexpr int IB[4] = {B0, B1, B2, B3};
+    double g[4];
 #pragma unroll
-    for (int e = 0; e < EPL; ++e) g = fma(x[e], y[e], g);
-    g = warp_sum(g);
-    const float gf = (float)g, nxf = (float)nx, nyf = (float)ny;
-    float relf = 0.f;
-    if (nxf > 0.f && nyf > 0.f) relf = fabsf(gf) * rsqrtf(nxf) * rsqrtf(nyf);
-    if (nx * ny > 1e-24 * nmax * nmax) off = fmax(off, (double)relf);
-    double c = 0.0, s = 1.0;            // pure swap: x_new = y, y_new = x
-    double mx = ny, my = nx;
-    if (relf > 1e-10f) {
-        const float zf = (float)(ny - nx) / (2.f * gf);
-        const float tf = copysignf(1.f, zf) / (fabsf(zf) + sqrtf(fmaf(zf, zf, 1.f)));
-        const double t = (double)tf;
-        const double u = fma(t, t, 1.0);
-        double c0 = (double)rsqrtf((float)u);
-        c0 = c0 * fma(-0.5 * u, c0 * c0, 1.5);
-        c0 = c0 * fma(-0.5 * u, c0 * c0, 1.5);
-        const double s0 = c0 * t;
-        // rotated pair (c0 x - s0 y, s0 x + c0 y), stored swapped
-        c = s0;
-        s = c0;
-        const double cc = c0 * c0, ss = s0 * s0, cs2 = 2.0 * c0 * s0 * g;
-        mx = fma(ss, nx, fma(cc, ny, cs2));      // |s0 x + c0 y|^2
-        my = fma(cc, nx, fma(ss, ny, -cs2));     // |c0 x - s0 y|^2
-    }
-    // x_new = c x + s y,  y_new = s x - c y   (swap: c = 0, s = 1 gives x_new = y, y_new = x)
-    const bool rotated = relf > 1e-10f;
+    for (int k = 0; k < 4; ++k) {
+        double g0 = 0.0, g1 = 0.0;
 #pragma unroll
-    for (int e = 0; e < EPL; ++e) {
-        const double xv = x[e], yv = y[e];
-        x[e] = fma(c, xv, s * yv);
-        y[e] = rotated ? fma(s, xv, -c * yv) : xv;
+        for (int e = 0; e < EPL; e += 2) {
+            g0 = fma(col[IA[k]][e], col[IB[k]][e], g0);
+            if (e + 1 < EPL) g1 = fma(col[IA[k]][e + 1], col[IB[k]][e + 1], g1);
+        }
+        g[k] = g0 + g1;
     }
-    nx = mx;
-    ny = my;
+    const bool h16 = (lane & 16) != 0, h8 = (lane & 8) != 0;
+    double k0 = sel(h16, g[2], g[0]) + __shfl_xor_sync(0xffffffffu, sel(h16, g[0], g[2]), 16);
+    double k1 = sel(h16, g[3], g[1]) + __shfl_xor_sync(0xffffffffu, sel(h16, g[1], g[3]), 16);
+    double gq = sel(h8, k1, k0) + __shfl_xor_sync(0xffffffffu, sel(h8, k0, k1), 8);
+    gq += __shfl_xor_sync(0xffffffffu, gq, 4);
+    gq += __shfl_xor_sync(0xffffffffu, gq, 2);
+    gq += __shfl_xor_sync(0xffffffffu, gq, 1);
+    // lanes 0-7: rotation 0, 8-15: rotation 1, 16-23: rotation 2, 24-31: rotation 3
+    const double nx = sel(h16, sel(h8, nrm[IA[3]], nrm[IA[2]]), sel(h8, nrm[IA[1]], nrm[IA[0]]));
+    const double ny = sel(h16, sel(h8, nrm[IB[3]], nrm[IB[2]]), sel(h8, nrm[IB[1]], nrm[IB[0]]));
+    double cq, sq, mxq, myq;
+    jacobi_angle(gq, nx, ny, nmax, off, cq, sq, mxq, myq);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const double c = __shfl_sync(0xffffffffu, cq, 8 * k);
+        const double s = __shfl_sync(0xffffffffu, sq, 8 * k);
+        nrm[IA[k]] = __shfl_sync(0xffffffffu, mxq, 8 * k);
+        nrm[IB[k]] = __shfl_sync(0xffffffffu, myq, 8 * k);
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) {
+            const double xv = col[IA[k]][e], yv = col[IB[k]][e];
+            col[IA[k]][e] = fma(c, xv, -s * yv);
+            col[IB[k]][e] = fma(s, xv, c * yv);
+        }
+    }
+}
+
+// all 16 pairs between block FB (columns FB..FB+3) and block SB
+template <int EPL, int FB, int SB>
+__device__ __forceinline__ void cross_blocks(double (&col)[8][EPL], double (&nrm)[8], double nmax, double& off,
+                                             int lane) {
+    rot4<EPL, FB + 0, SB + 0, FB + 1, SB + 1, FB + 2, SB + 2, FB + 3, SB + 3>(col, nrm, nmax, off, lane);
+    rot4<EPL, FB + 0, SB + 1, FB + 1, SB + 2, FB + 2, SB + 3, FB + 3, SB + 0>(col, nrm, nmax, off, lane);
+    rot4<EPL, FB + 0, SB + 2, FB + 1, SB + 3, FB + 2, SB + 0, FB + 3, SB + 1>(col, nrm, nmax, off, lane);
+    rot4<EPL, FB + 0, SB + 3, FB + 1, SB + 0, FB + 2, SB + 1, FB + 3, SB + 2>(col, nrm, nmax, off, lane);
+}
+
+template <int EPL, int B>
+__device__ __forceinline__ void put_block(double (*slot)[32 * EPL], double* nslot, const double (&col)[8][EPL],
+                                          const double (&nrm)[8], int lane) {
+#pragma unroll
+    for (int k = 0; k < EIG_C; ++k) {
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) slot[k][lane + 32 * e] = col[B + k][e];
+    }
+    if (lane < EIG_C) {
+        double v = nrm[B];
+        if (lane == 1) v = nrm[B + 1];
+        if (lane == 2) v = nrm[B + 2];
+        if (lane == 3) v = nrm[B + 3];
+        nslot[lane] = v;
+    }
+}
+template <int EPL, int B>
+__device__ __forceinline__ void get_block(uint32_t slot_addr, uint32_t nslot_addr, double (&col)[8][EPL],
+                                          double (&nrm)[8], int lane) {
+#pragma unroll
+    for (int k = 0; k < EIG_C; ++k) {
+#pragma unroll
+        for (int e = 0; e < EPL; ++e)
+            col[B + k][e] = dsmem_ld(slot_addr + (uint32_t)((k * 32 * EPL + lane + 32 * e) * 8));
+        nrm[B + k] = dsmem_ld(nslot_addr + (uint32_t)(k * 8));
+    }
+}
+
+// One iteration = two rounds of the odd-even transposition ordering on BLOCK
+// positions.  On entry block FB sits at position 2w, block SB at 2w+1 (w = warp
+// index in the cluster); the same holds on exit.  Rotations never move data: the
+// trade of places is a relabelling, only the blocks that cross a warp boundary
+// travel (one block out, one block in, per round).
+template <int EPL, int FB, int SB>
+__device__ __forceinline__ void jacobi_iteration(EigSmem<EPL>& sm, double (&col)[8][EPL], double (&nrm)[8],
+                                                 double nmax, double& off, int w, int lw, int rank, int lane,
+                                                 int M) {
+    // even round: positions (2w, 2w+1); afterwards SB is at 2w, FB at 2w+1
+    cross_blocks<EPL, FB, SB>(col, nrm, nmax, off, lane);
+    // odd round: positions (2w+1, 2w+2) = (FB, first block of warp w+1)
+    put_block<EPL, SB>(sm.slotA[lw], sm.normA[lw], col, nrm, lane);
+    cluster_barrier();
+    if (w + 1 < M) {
+        const int nlw = (lw + 1) % EIG_WARPS;
+        const int nrk = (lw + 1 == EIG_WARPS) ? rank + 1 : rank;
+        get_block<EPL, SB>(dsmem_addr(&sm.slotA[nlw][0][0], nrk), dsmem_addr(&sm.normA[nlw][0], nrk), col, nrm, lane);
+        cross_blocks<EPL, FB, SB>(col, nrm, nmax, off, lane);
+        // afterwards SB is at 2w+1 (stays), FB at 2w+2 (goes to warp w+1)
+        put_block<EPL, FB>(sm.slotB[lw], sm.normB[lw], col, nrm, lane);
+    }
+    cluster_barrier();
+    if (w + 1 == M) {
+        // the last warp sat the odd round out: FB is still at 2w+1, register block SB is free
+#pragma unroll
+        for (int k = 0; k < EIG_C; ++k) {
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) col[SB + k][e] = col[FB + k][e];
+            nrm[SB + k] = nrm[FB + k];
+        }
+    }
+    if (w == 0) {
+        // position 0 sat the odd round out, parked in this warp's own slotA
+        get_block<EPL, FB>(dsmem_addr(&sm.slotA[lw][0][0], rank), dsmem_addr(&sm.normA[lw][0], rank), col, nrm, lane);
+    } else {
+        const int plw = (lw + EIG_WARPS - 1) % EIG_WARPS;
+        const int prk = (lw == 0) ? rank - 1 : rank;
+        get_block<EPL, FB>(dsmem_addr(&sm.slotB[plw][0][0], prk), dsmem_addr(&sm.normB[plw][0], prk), col, nrm, lane);
+    }
 }
 
 // Grid = S * EPL CTAs, cluster = EPL CTAs, EIG_NT threads, dynamic smem = sizeof(EigSmem<EPL>).
@@ -120,11 +259,12 @@ template <int EPL>
 __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
     constexpr int N2 = 32 * EPL;
     constexpr int ELL = 16 * EPL;
-    constexpr int M = N2 / 2;                 // warps in the cluster
+    constexpr int M = N2 / (2 * EIG_C);       // warps in the cluster = EPL * EIG_WARPS
     extern __shared__ __align__(16) unsigned char smem_raw[];
     EigSmem<EPL>& sm = *reinterpret_cast<EigSmem<EPL>*>(smem_raw);
-    cg::cluster_group cluster = cg::this_cluster();
-    const int rank = (EPL == 1) ? 0 : (int)cluster.block_rank();
+    uint32_t rank_u;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank_u));
+    const int rank = (int)rank_u;
     const int s = blockIdx.x / EPL;
     const int lw = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int w = rank * EIG_WARPS + lw;
@@ -137,162 +277,137 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
     const int q_head = sl.q_head, q_len = sl.q_len;
     const unsigned long long last_dump = sl.last_dump;
     const double thr = sl.error;
-    auto sync_all = [&]() {
-        if (EPL == 1) __syncthreads();
-        else cluster.sync();
-    };
 
-    // ---- load: columns 2w, 2w+1 of the symmetrised, masked Gram ------------------
+    // ---- load: columns 8w .. 8w+7 of the symmetrised, masked Gram -------------------
     const unsigned char* mk = A.mask + (size_t)s * ELL;
     auto dead = [&](int i) -> bool {
         if (i < ELL) return false;
         const int r = i - ELL;
         return r >= A.n_rows || mk[r] != 0;
     };
-    double a[EPL], b[EPL];
+    double col[8][EPL];
+    double nrm[8];
     {
         const float* G0 = A.Gp + (size_t)s * A.KS * N2 * N2;
-        const int ja = 2 * w, jb = 2 * w + 1;
-        const bool da = dead(ja), db = dead(jb);
 #pragma unroll
-        for (int e = 0; e < EPL; ++e) {
-            const int i = lane + 32 * e;
-            double va = 0.0, vb = 0.0;
-            if (!dead(i)) {
-                for (int k = 0; k < A.KS; ++k) {
-                    const float* G = G0 + (size_t)k * N2 * N2;
-                    va += (double)G[(size_t)ja * N2 + i] + (double)G[(size_t)i * N2 + ja];
-                    vb += (double)G[(size_t)jb * N2 + i] + (double)G[(size_t)i * N2 + jb];
+        for (int k = 0; k < 8; ++k) {
+            const int j = 8 * w + k;
+            const bool dj = dead(j);
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) {
+                const int i = lane + 32 * e;
+                double v = 0.0;
+                if (!dj && !dead(i)) {
+                    for (int q = 0; q < A.KS; ++q) {
+                        const float* G = G0 + (size_t)q * N2 * N2;
+                        v += (double)G[(size_t)j * N2 + i] + (double)G[(size_t)i * N2 + j];
+                    }
                 }
+                col[k][e] = 0.5 * v;
             }
-            a[e] = da ? 0.0 : 0.5 * va;
-            b[e] = db ? 0.0 : 0.5 * vb;
         }
     }
 
     // ---- sweeps -------------------------------------------------------------------------
-    double na = 0.0, nb = 0.0;
     int sweeps_done = 0;
     double off = 0.0;
+    const uint32_t ro0 = dsmem_addr(sm.red_off, 0), rn0 = dsmem_addr(sm.red_nmax, 0);
     for (int sweep = 0; sweep < A.max_sweeps; ++sweep) {
-        na = 0.0;
-        nb = 0.0;
+        double nm = 0.0;
 #pragma unroll
-        for (int e = 0; e < EPL; ++e) {
-            na = fma(a[e], a[e], na);
-            nb = fma(b[e], b[e], nb);
+        for (int k = 0; k < 8; ++k) {
+            double t = 0.0;
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) t = fma(col[k][e], col[k][e], t);
+            nrm[k] = t;
         }
-        na = warp_sum(na);
-        nb = warp_sum(nb);
-        // cluster-wide: largest column norm^2 and last sweep's largest off-diagonal cosine
-        {
-            double* ro = (EPL == 1) ? sm.red_off : cluster.map_shared_rank(sm.red_off, 0);
-            double* rn = (EPL == 1) ? sm.red_nmax : cluster.map_shared_rank(sm.red_nmax, 0);
-            if (lane == 0) {
-                ro[w] = off;
-                rn[w] = fmax(na, nb);
-            }
-            sync_all();
-            double o = 0.0, nm = 0.0;
-            for (int i = lane; i < M; i += 32) {
-                o = fmax(o, ro[i]);
-                nm = fmax(nm, rn[i]);
-            }
-            o = warp_max(o);
-            nm = warp_max(nm);
-            sync_all();                         // everyone has read before the arrays are rewritten
-            if (sweep > 0 && o <= A.tol) break;
-            off = 0.0;
-            const double nmax = nm;
-            // ---- one sweep = N2 rounds, two per iteration -----------------------------
-            for (int it = 0; it < M; ++it) {
-                // positions (2w, 2w+1)
-                jacobi_pair<EPL>(a, b, na, nb, nmax, off);
-                // positions (2w+1, 2w+2): fetch the right neighbour's first column
 #pragma unroll
-                for (int e = 0; e < EPL; ++e) sm.slotA[lw][lane + 32 * e] = a[e];
-                if (lane == 0) sm.normA[lw] = na;
-                sync_all();
-                double c2[EPL];
-                double nc = 0.0;
-                const bool has_right = (w + 1 < M);
-                if (has_right) {
-                    const int nlw = (lw + 1) % EIG_WARPS;
-                    const int nrk = (lw + 1 == EIG_WARPS) ? rank + 1 : rank;
-                    const double* src = (EPL == 1 || nrk == rank) ? &sm.slotA[nlw][0]
-                                                                    : cluster.map_shared_rank(&sm.slotA[nlw][0], nrk);
-                    const double* nsrc = (EPL == 1 || nrk == rank) ? &sm.normA[nlw]
-                                                                     : cluster.map_shared_rank(&sm.normA[nlw], nrk);
+        for (int o = 16; o > 0; o >>= 1)
 #pragma unroll
-                    for (int e = 0; e < EPL; ++e) c2[e] = src[lane + 32 * e];
-                    nc = *nsrc;
-                    jacobi_pair<EPL>(b, c2, nb, nc, nmax, off);
-                    // now b = position 2w+1, c2 = position 2w+2 (goes back to the right neighbour)
+            for (int k = 0; k < 8; ++k) nrm[k] += __shfl_xor_sync(0xffffffffu, nrm[k], o);
 #pragma unroll
-                    for (int e = 0; e < EPL; ++e) sm.slotB[lw][lane + 32 * e] = c2[e];
-                    if (lane == 0) sm.normB[lw] = nc;
-                }
-                sync_all();
-                if (w > 0) {
-                    const int plw = (lw + EIG_WARPS - 1) % EIG_WARPS;
-                    const int prk = (lw == 0) ? rank - 1 : rank;
-                    const double* src = (EPL == 1 || prk == rank) ? &sm.slotB[plw][0]
-                                                                    : cluster.map_shared_rank(&sm.slotB[plw][0], prk);
-                    const double* nsrc = (EPL == 1 || prk == rank) ? &sm.normB[plw]
-                                                                     : cluster.map_shared_rank(&sm.normB[plw], prk);
-#pragma unroll
-                    for (int e = 0; e < EPL; ++e) a[e] = src[lane + 32 * e];
-                    na = *nsrc;
-                }
-                // warp 0 keeps its own first column (position 0 sits this round out)
-            }
-            sweeps_done = sweep + 1;
+        for (int k = 0; k < 8; ++k) nm = fmax(nm, nrm[k]);
+        // cluster-wide: largest column norm^2 and the last sweep's largest cosine
+        off = warp_max(off);
+        if (lane == 0) {
+            dsmem_st(ro0 + (uint32_t)(w * 8), off);
+            dsmem_st(rn0 + (uint32_t)(w * 8), nm);
         }
+        cluster_barrier();
+        double o = 0.0;
+        nm = 0.0;
+        for (int i = lane; i < M; i += 32) {
+            o = fmax(o, dsmem_ld(ro0 + (uint32_t)(i * 8)));
+            nm = fmax(nm, dsmem_ld(rn0 + (uint32_t)(i * 8)));
+        }
+        o = warp_max(o);
+        nm = warp_max(nm);
+        cluster_barrier();                      // all have read before the arrays are rewritten
+        if (sweep > 0 && o <= A.tol) break;
+        off = 0.0;
+        // pairs inside each block (three stages of four independent rotations)
+        rot4<EPL, 0, 1, 2, 3, 4, 5, 6, 7>(col, nrm, nm, off, lane);
+        rot4<EPL, 0, 2, 1, 3, 4, 6, 5, 7>(col, nrm, nm, off, lane);
+        rot4<EPL, 0, 3, 1, 2, 4, 7, 5, 6>(col, nrm, nm, off, lane);
+        // block pairs: 2M block positions, 2M rounds, two per iteration
+#pragma unroll 1
+        for (int it = 0; it < M; ++it) jacobi_iteration<EPL, 0, 4>(sm, col, nrm, nm, off, w, lw, rank, lane, M);
+        sweeps_done = sweep + 1;
     }
 
-    // ---- eigenvalues per position, replicated into every CTA ---------------------------
-    na = 0.0;
-    nb = 0.0;
+    // ---- eigenvalues per column id, replicated into every CTA ---------------------------
+    double lamv[8];
 #pragma unroll
-    for (int e = 0; e < EPL; ++e) {
-        na = fma(a[e], a[e], na);
-        nb = fma(b[e], b[e], nb);
+    for (int k = 0; k < 8; ++k) {
+        double t = 0.0;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) t = fma(col[k][e], col[k][e], t);
+        lamv[k] = t;
     }
-    na = sqrt(warp_sum(na));
-    nb = sqrt(warp_sum(nb));
-    sync_all();
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) lamv[k] += __shfl_xor_sync(0xffffffffu, lamv[k], o);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) lamv[k] = sqrt(lamv[k]);
     if (lane < EPL) {
-        double* dst = (EPL == 1) ? sm.lam : cluster.map_shared_rank(sm.lam, lane);
-        dst[2 * w] = na;
-        dst[2 * w + 1] = nb;
+        const uint32_t dst = dsmem_addr(sm.lam, lane);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) dsmem_st(dst + (uint32_t)((8 * w + k) * 8), lamv[k]);
     }
-    sync_all();
-    // rank (descending, ties by position) of my two columns
-    int ra = 0, rb = 0;
+    cluster_barrier();
+    // rank (descending, ties by column id) of my eight columns
+    int rk[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) rk[k] = 0;
     for (int i = lane; i < N2; i += 32) {
         const double v = sm.lam[i];
-        ra += (v > na) || (v == na && i < 2 * w);
-        rb += (v > nb) || (v == nb && i < 2 * w + 1);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) rk[k] += (v > lamv[k]) || (v == lamv[k] && i < 8 * w + k);
     }
-    ra = __reduce_add_sync(0xffffffffu, ra);
-    rb = __reduce_add_sync(0xffffffffu, rb);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) rk[k] = __reduce_add_sync(0xffffffffu, rk[k]);
     if (lane < EPL) {
-        double* dst = (EPL == 1) ? &sm.cut : cluster.map_shared_rank(&sm.cut, lane);
-        if (ra == ELL) *dst = na;
-        if (rb == ELL) *dst = nb;
+        const uint32_t dst = dsmem_addr(&sm.cut, lane);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            if (rk[k] == ELL) dsmem_st(dst, lamv[k]);
     }
-    sync_all();
+    cluster_barrier();
     const double cut = sm.cut;
 
     // ---- outputs -------------------------------------------------------------------------
     const int src_plane = sl.cur;
     float* Ts = A.T + (size_t)s * ELL * N2;
-    auto emit = [&](const double (&col)[EPL], double lam, int r) {
-        if (r >= ELL) return;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int r = rk[k];
+        if (r >= ELL) continue;
+        const double lam = lamv[k];
         const double s2v = fmax(lam - cut, 0.0);
         const double coef = (lam > 0.0 && s2v > 0.0) ? sqrt(s2v / lam) / lam : 0.0;
 #pragma unroll
-        for (int e = 0; e < EPL; ++e) Ts[(size_t)r * N2 + lane + 32 * e] = (float)(coef * col[e]);
+        for (int e = 0; e < EPL; ++e) Ts[(size_t)r * N2 + lane + 32 * e] = (float)(coef * col[k][e]);
         if (lane == 0) {
             const bool dumped = s2v >= thr;
             int slot = -1;
@@ -305,9 +420,7 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
             A.dump_slot[(size_t)s * ELL + r] = slot;
             A.s2[(size_t)s * ELL + r] = dumped ? 0.0 : s2v;
         }
-    };
-    emit(a, na, ra);
-    emit(b, nb, rb);
+    }
     if (w == 0) {
         int nd = 0;
         for (int i = lane; i < N2; i += 32) nd += (fmax(sm.lam[i] - cut, 0.0) >= thr) ? 1 : 0;
@@ -325,6 +438,7 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
             sl.sweeps = sweeps_done;
         }
     }
+    cluster_barrier();                          // no CTA leaves while its shared memory may still be read
 }
 
 }  // namespace mused
