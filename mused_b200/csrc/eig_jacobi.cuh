@@ -119,7 +119,7 @@ __device__ __forceinline__ void jacobi_angle(double g, double nx, double ny, dou
     const double u = fma(t, t, 1.0);
     double c0 = rsqrt_approx(u);
     c0 = c0 * fma(-0.5 * u, c0 * c0, 1.5);
-    c0 = c0 * fma(-0.5 * u, c0 * c0, 1.5);
+    c0 = c0 * fma(-0.5 * u, c0 * c0, 1.5);     // 20 -> 40 -> 80 bits
     c = sel(apply, c0, 1.0);
     s = sel(apply, c0 * t, 0.0);
     const double cc = c * c, ss = s * s, cs2 = (c + c) * s * g;
