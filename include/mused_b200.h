@@ -128,6 +128,30 @@ int mused_swfd_kernel_ms(mused_swfd_t* h, int enable, double* ms5, int64_t* chun
 int mused_swfd_profile(mused_swfd_t* h, uint64_t* cycles, int64_t n_inst_cap);
 
 /* ---------------------------------------------------------------------------
+ * Column-sharded mode (schedule = BATCHED): rank r holds columns
+ * [lo_r, hi_r) of every row and of the sketch (cfg.d = hi_r - lo_r).  The caller
+ * (mused_b200/sharded.py, torch.distributed / NCCL) drives one chunk in phases and
+ * runs the two exchanges of the path on the device buffers the library exposes:
+ *   stage (rows of the open chunk, <= room)
+ *   -> allreduce-sum norm2[ell]            (routing rule X@X.T >= threshold, seq_based_swfd.py:77)
+ *   -> chunk_gram                          (bookkeeping, tcgen05 Gram of the local columns)
+ *   -> allreduce-sum gram[S][2l][2l]       (the one real exchange per shrink)
+ *   -> chunk_finish                        (replicated eigensolve, local rotate)
+ * and a query as  get_begin -> allreduce-sum query_gram (when n_stack > 0) -> get_finish.
+ * Every decision depends on replicated scalars only, so all ranks stay in lock-step.
+ * ------------------------------------------------------------------------- */
+int mused_swfd_chunk_room(mused_swfd_t* h, int64_t* room, int64_t* pending);
+int mused_swfd_stage(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld, int dtype, int where,
+                     void* stream);
+int mused_swfd_chunk_gram(mused_swfd_t* h, void* stream);
+int mused_swfd_chunk_finish(mused_swfd_t* h, void* stream);
+int mused_swfd_exchange_buffers(mused_swfd_t* h, double** norm2, int64_t* norm2_count, double** gram,
+                                int64_t* gram_count, double** query_gram, int64_t* query_gram_count);
+int mused_swfd_get_begin(mused_swfd_t* h, int32_t* level, int32_t* n_stack, void* stream);
+int mused_swfd_get_finish(mused_swfd_t* h, double* sketch, double* sigma2, double* vt, double* delta,
+                          int where, void* stream);
+
+/* ---------------------------------------------------------------------------
  * One Frequent Directions instance with row buffer and dump.
  * Replaces swfd/frequent_directions.py:96-153 (FrequentDirectionsWithDump) and,
  * with error = +inf and explicit batches, :79-93 (RobustFrequentDirections).

@@ -40,6 +40,8 @@ SYMBOLS = [
     "mused_count_launches", "mused_swfd_profile", "mused_swfd_timing", "mused_swfd_kernel_ms",
     "mused_swfd_create", "mused_swfd_destroy", "mused_swfd_fit", "mused_swfd_get",
     "mused_swfd_size", "mused_swfd_time", "mused_swfd_debug", "mused_swfd_queue_capacity",
+    "mused_swfd_chunk_room", "mused_swfd_stage", "mused_swfd_chunk_gram", "mused_swfd_chunk_finish",
+    "mused_swfd_exchange_buffers", "mused_swfd_get_begin", "mused_swfd_get_finish",
     "mused_fd_create", "mused_fd_destroy", "mused_fd_fit", "mused_fd_fit_batches",
     "mused_fd_dump", "mused_fd_flush", "mused_fd_get",
     "mused_assign", "mused_topk_adjacency", "mused_contingency",
@@ -63,6 +65,14 @@ def load():
     lib.mused_swfd_profile.argtypes = [vp, vp, i64]
     lib.mused_swfd_timing.argtypes = [vp, C.c_int, C.POINTER(dbl), C.POINTER(i64), C.POINTER(i64)]
     lib.mused_swfd_kernel_ms.argtypes = [vp, C.c_int, C.POINTER(dbl), C.POINTER(i64), C.POINTER(i64)]
+    lib.mused_swfd_chunk_room.argtypes = [vp, C.POINTER(i64), C.POINTER(i64)]
+    lib.mused_swfd_stage.argtypes = [vp, vp, i64, i64, C.c_int, C.c_int, vp]
+    lib.mused_swfd_chunk_gram.argtypes = [vp, vp]
+    lib.mused_swfd_chunk_finish.argtypes = [vp, vp]
+    lib.mused_swfd_exchange_buffers.argtypes = [vp, C.POINTER(vp), C.POINTER(i64), C.POINTER(vp), C.POINTER(i64),
+                                                C.POINTER(vp), C.POINTER(i64)]
+    lib.mused_swfd_get_begin.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), vp]
+    lib.mused_swfd_get_finish.argtypes = [vp, vp, vp, vp, C.POINTER(dbl), C.c_int, vp]
     lib.mused_swfd_create.argtypes = [C.POINTER(vp), C.POINTER(SwfdCfg)]
     lib.mused_swfd_destroy.argtypes = [vp]
     lib.mused_swfd_fit.argtypes = [vp, vp, i64, i64, C.c_int, C.c_int, vp]

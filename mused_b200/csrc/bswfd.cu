@@ -129,6 +129,19 @@ __global__ void __launch_bounds__(256) k_bbook(BDev D, int n, unsigned long long
     }
 }
 
+// split-K reduction of K2's partial Grams, float64, fixed order (deterministic)
+__global__ void __launch_bounds__(256) k_gram_reduce(BDev D) {
+    const size_t per = (size_t)D.n2 * D.n2;
+    const size_t tot = (size_t)D.S * per;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < tot; e += (size_t)gridDim.x * blockDim.x) {
+        const size_t s = e / per, ij = e - s * per;
+        const float* p = D.Gp + s * D.KS * per + ij;
+        double acc = 0.0;
+        for (int k = 0; k < D.KS; ++k) acc += (double)p[(size_t)k * per];
+        D.G[e] = acc;
+    }
+}
+
 // ---------------------------------------------------------------------------
 // K4: shrink + rotate (frequent_directions.py:86-93, :58):
 //   out[r][c] = sum_k T[r][k] * R[k][c],  R = [sketch(src plane); chunk]
@@ -264,6 +277,7 @@ struct BEngine {
     QueryScratch Q;
     double *o_sketch = nullptr, *o_vt = nullptr, *o_s2 = nullptr, *o_delta = nullptr;
     std::vector<void*> allocs;
+    int q_slot = 0, q_ng = 0;         // pending query (get_begin -> get_finish)
     bool timing = false;
     std::vector<cudaEvent_t> ev[5];
     double timed_ms[5] = {0, 0, 0, 0, 0};
@@ -357,6 +371,7 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     A_(D.norm2, (size_t)ell);
     A_(D.mask, Sa * ell);
     A_(D.Gp, Sa * KS * D.n2 * D.n2);
+    A_(D.G, Sa * D.n2 * D.n2);
     A_(D.T, Sa * ell * D.n2);
     A_(D.s2, Sa * ell);
     A_(D.dump_slot, Sa * ell);
@@ -369,6 +384,7 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     Q.ng_max = D.ell + D.capn + 1;
     Q.ng_max += Q.ng_max & 1;
     Q.lda = Q.ng_max;
+    Q.rel_thr = 1e-11;     // the fp32-product Grams upstream carry ~1e-6; 1e-11 leaves eigenvalues exact to ~1e-20
     A_(Q.M, (size_t)Q.ng_max * d);
     A_(Q.G, (size_t)Q.lda * Q.lda);
     A_(Q.Vq, (size_t)Q.lda * Q.lda);
@@ -439,8 +455,7 @@ static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t 
     }
     EigArgs A;
     A.slots = E.D.slots;
-    A.Gp = E.D.Gp;
-    A.KS = E.D.KS;
+    A.G = E.D.G;
     A.ell = E.D.ell;
     A.n2 = E.D.n2;
     A.capn = E.D.capn;
@@ -470,29 +485,44 @@ static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t 
     return 0;
 }
 
-// fold the staged chunk (E.pend rows, times done+1 ..) into every FD instance
-static int process_chunk(BEngine& E, cudaStream_t st) {
+// Fold the staged chunk (E.pend rows, times done+1 ..) into every FD instance, in two
+// phases: everything up to the Gram (a column-sharded run adds the other shards'
+// Grams in between), then eigensolve + rotate.
+int bengine_chunk_gram(BEngine* Ep, cudaStream_t st) {
+    BEngine& E = *Ep;
     const int n = E.pend;
-    if (n == 0) return 0;
+    if (n == 0 || E.D.S == 0) return 0;
     BDev& D = E.D;
     const unsigned long long t_a = E.done + 1ull;
     int rc = 0;
+    E.mark(1, st);
+    k_bbook<<<D.S, 256, 0, st>>>(D, n, t_a);
+    MUSED_CUDA(cudaGetLastError());
+    E.mark(1, st);
+    E.mark(2, st);
+    switch (D.ell) {
+        case 16: rc = launch_gram<32>(E, st); break;
+        case 32: rc = launch_gram<64>(E, st); break;
+        case 64: rc = launch_gram<128>(E, st); break;
+        default: rc = launch_gram<256>(E, st); break;
+    }
+    if (rc) return rc;
+    k_gram_reduce<<<std::min<long long>(((long long)D.S * D.n2 * D.n2 + 255) / 256, 8ll * E.sm_count), 256, 0, st>>>(D);
+    MUSED_CUDA(cudaGetLastError());
+    E.mark(2, st);
+    mused_count_launches(3);
+    return 0;
+}
+
+int bengine_chunk_finish(BEngine* Ep, cudaStream_t st) {
+    BEngine& E = *Ep;
+    const int n = E.pend;
+    if (n == 0) return 0;
+    BDev& D = E.D;
+    int rc = 0;
     if (D.S > 0) {
-        E.mark(1, st);
-        k_bbook<<<D.S, 256, 0, st>>>(D, n, t_a);
-        MUSED_CUDA(cudaGetLastError());
-        E.mark(1, st);
-        E.mark(2, st);
-        switch (D.ell) {
-            case 16: rc = launch_gram<32>(E, st); break;
-            case 32: rc = launch_gram<64>(E, st); break;
-            case 64: rc = launch_gram<128>(E, st); break;
-            default: rc = launch_gram<256>(E, st); break;
-        }
-        if (rc) return rc;
-        E.mark(2, st);
+        const unsigned long long t_end = E.done + (unsigned long long)n;
         E.mark(3, st);
-        const unsigned long long t_end = t_a + (unsigned long long)n - 1ull;
         switch (D.ell) {
             case 16: rc = launch_eig<1>(E, n, t_end, st); break;
             case 32: rc = launch_eig<2>(E, n, t_end, st); break;
@@ -505,12 +535,18 @@ static int process_chunk(BEngine& E, cudaStream_t st) {
         k_brotate<<<dim3((unsigned)((D.d + RT - 1) / RT), (unsigned)((D.ell + RT - 1) / RT), (unsigned)D.S), 256, 0, st>>>(D);
         MUSED_CUDA(cudaGetLastError());
         E.mark(4, st);
-        mused_count_launches(4);
+        mused_count_launches(2);
     }
     if (E.timing) { E.timed_chunks += 1; E.timed_rows += n; }
     E.done += (unsigned long long)n;
     E.pend = 0;
     return 0;
+}
+
+static int process_chunk(BEngine& E, cudaStream_t st) {
+    int rc = bengine_chunk_gram(&E, st);
+    if (rc) return rc;
+    return bengine_chunk_finish(&E, st);
 }
 
 // rows the current chunk may still take before it must be processed
@@ -614,23 +650,25 @@ static int b_copy_out(double* dst, const double* src, size_t n, int where, cudaS
     return 0;
 }
 
-int bengine_get(BEngine* Ep, double* sketch, double* sigma2, double* vt, double* delta, int* level,
-                int where, cudaStream_t st) {
+// SeqBasedSWFD.get, first half: level choice (seq_based_swfd.py:83-98), stack
+// [C; snapshots] of the chosen level and its float64 Gram.  *ng = rows of the
+// stack, 0 when the level has no snapshots (no Gram needed).
+int bengine_get_begin(BEngine* Ep, int* level, int* ng_out, cudaStream_t st) {
     BEngine& E = *Ep;
     BDev& D = E.D;
     if (E.n_levels == 0) {
         set_error("SeqBasedSWFD has zero levels (R <= 1): get() is undefined");
         return MUSED_ERR_STATE;
     }
+    MUSED_REQUIRE(E.pend == 0, "get_begin: the open chunk must be closed first");
     MUSED_CUDA(cudaSetDevice(E.device));
-    int rc = process_chunk(E, st);      // get() closes the open chunk (the reference flushes on get, too)
-    if (rc) return rc;
     MUSED_CUDA(cudaStreamSynchronize(st));
     std::vector<BSlot> sl;
+    int rc = 0;
     if ((rc = b_read_slots(E, sl))) return rc;
     int rj = 0;
     const unsigned long long time = E.time, N = D.N;
-    for (int j = 0; j < E.n_levels; ++j) {        // seq_based_swfd.py:83-98
+    for (int j = 0; j < E.n_levels; ++j) {
         const int s = b_fd_slot(E, j);
         if (sl[s].q_len == 0) break;
         unsigned long long head_s = 0;
@@ -639,18 +677,34 @@ int bengine_get(BEngine* Ep, double* sketch, double* sigma2, double* vt, double*
     }
     if (level) *level = rj;
     const int s = b_fd_slot(E, rj);
-    const size_t ld_out = (size_t)D.ell * D.d;
-    if (sl[s].q_len == 0) {
-        k_bfd_out<<<E.sm_count, 256, 0, st>>>(D, s, E.o_sketch, E.o_s2, vt ? E.o_vt : nullptr, E.o_delta);
-        MUSED_CUDA(cudaGetLastError());
-        mused_count_launches(1);
-    } else {
+    E.q_slot = s;
+    E.q_ng = 0;
+    if (sl[s].q_len != 0) {
         const int ng = D.ell + sl[s].q_len;
         MUSED_REQUIRE(ng + (ng & 1) <= E.Q.ng_max, "internal: stack of %d rows exceeds scratch %d", ng, E.Q.ng_max);
         k_bgather<<<std::min(ng, 4 * E.sm_count), 256, 0, st>>>(D, s, E.Q.M);
         MUSED_CUDA(cudaGetLastError());
         mused_count_launches(1);
-        if ((rc = merge_query(E.Q, ng, D.d, D.ell, E.sm_count, E.o_sketch, vt ? E.o_vt : nullptr, E.o_s2, st))) return rc;
+        if ((rc = merge_query_gram(E.Q, ng, D.d, E.sm_count, st))) return rc;
+        E.q_ng = ng;
+    }
+    if (ng_out) *ng_out = E.q_ng;
+    return 0;
+}
+
+int bengine_get_finish(BEngine* Ep, double* sketch, double* sigma2, double* vt, double* delta, int where,
+                       cudaStream_t st) {
+    BEngine& E = *Ep;
+    BDev& D = E.D;
+    int rc = 0;
+    const int s = E.q_slot;
+    const size_t ld_out = (size_t)D.ell * D.d;
+    if (E.q_ng == 0) {
+        k_bfd_out<<<E.sm_count, 256, 0, st>>>(D, s, E.o_sketch, E.o_s2, vt ? E.o_vt : nullptr, E.o_delta);
+        MUSED_CUDA(cudaGetLastError());
+        mused_count_launches(1);
+    } else {
+        if ((rc = merge_query_solve(E.Q, E.q_ng, D.d, D.ell, E.sm_count, E.o_sketch, vt ? E.o_vt : nullptr, E.o_s2, st))) return rc;
         MUSED_CUDA(cudaMemsetAsync(E.o_delta, 0, sizeof(double), st));
     }
     if ((rc = b_copy_out(sketch, E.o_sketch, ld_out, where, st))) return rc;
@@ -658,6 +712,58 @@ int bengine_get(BEngine* Ep, double* sketch, double* sigma2, double* vt, double*
     if ((rc = b_copy_out(vt, E.o_vt, ld_out, where, st))) return rc;
     if (delta) MUSED_CUDA(cudaMemcpyAsync(delta, E.o_delta, sizeof(double), cudaMemcpyDeviceToHost, st));
     MUSED_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int bengine_get(BEngine* Ep, double* sketch, double* sigma2, double* vt, double* delta, int* level,
+                int where, cudaStream_t st) {
+    BEngine& E = *Ep;
+    if (E.n_levels == 0) {
+        set_error("SeqBasedSWFD has zero levels (R <= 1): get() is undefined");
+        return MUSED_ERR_STATE;
+    }
+    MUSED_CUDA(cudaSetDevice(E.device));
+    int rc = process_chunk(E, st);      // get() closes the open chunk (the reference flushes on get, too)
+    if (rc) return rc;
+    int ng = 0;
+    if ((rc = bengine_get_begin(Ep, level, &ng, st))) return rc;
+    return bengine_get_finish(Ep, sketch, sigma2, vt, delta, where, st);
+}
+
+long long bengine_room(BEngine* E) { return chunk_room(*E); }
+int bengine_pending(BEngine* E) { return E->pend; }
+int bengine_ell(BEngine* E) { return E->D.ell; }
+
+int bengine_buffers(BEngine* E, double** norm2, double** G, long long* g_count, double** QG, long long* qg_count) {
+    if (norm2) *norm2 = E->D.norm2;
+    if (G) *G = E->D.G;
+    if (g_count) *g_count = (long long)E->D.S * E->D.n2 * E->D.n2;
+    if (QG) *QG = E->Q.G;
+    if (qg_count) *qg_count = (long long)E->Q.lda * E->Q.lda;
+    return 0;
+}
+
+// K1 only: stage m (<= room) rows into the open chunk
+int bengine_stage(BEngine* Ep, const void* rows, long long m, long long ld, int dtype, int where, cudaStream_t st) {
+    BEngine& E = *Ep;
+    const size_t es = b_dtype_size(dtype);
+    MUSED_REQUIRE(es != 0, "unknown dtype %d", dtype);
+    MUSED_REQUIRE(m >= 0 && m <= chunk_room(E), "stage: %lld rows do not fit the open chunk (room %lld)", m, chunk_room(E));
+    MUSED_REQUIRE(ld >= E.D.d && (rows || m == 0), "bad rows / ld");
+    if (m == 0) return 0;
+    MUSED_CUDA(cudaSetDevice(E.device));
+    const void* dev = rows;
+    long long dev_ld = ld;
+    if (where == MUSED_HOST) {
+        MUSED_REQUIRE((size_t)m * E.D.d * es <= E.raw_bytes, "stage: block too large");
+        MUSED_CUDA(cudaMemcpy2DAsync(E.raw, (size_t)E.D.d * es, rows, (size_t)ld * es, (size_t)E.D.d * es, (size_t)m, cudaMemcpyHostToDevice, st));
+        dev = E.raw;
+        dev_ld = E.D.d;
+    }
+    int rc = stage_rows(E, dev, m, dev_ld, dtype, st);
+    if (rc) return rc;
+    E.time += (unsigned long long)m;
+    if (where == MUSED_HOST) MUSED_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
 

@@ -18,7 +18,8 @@ struct BDev {
     float *xhi, *xlo;          // [ell][d] the chunk being assembled / processed
     double* norm2;             // [ell]
     unsigned char* mask;       // [S][ell] 1 = chunk row is a raw snapshot at this instance's level
-    float* Gp;                 // [S][KS][n2][n2]
+    float* Gp;                 // [S][KS][n2][n2] split-K partials of K2
+    double* G;                 // [S][n2][n2] their float64 sum (the buffer a column-sharded run allreduces)
     float* T;                  // [S][ell][n2]
     double* s2;                // [S][ell]
     int* dump_slot;            // [S][ell]
@@ -44,12 +45,32 @@ int bengine_debug(BEngine* E, double* scal, double* sigma2, unsigned long long* 
 // chunks processed.  enable: 1 arm+reset, 0 disarm+reset, -1 read only.
 int bengine_timing(BEngine* E, int enable, double* ms, long long* chunks, long long* rows);
 
+// Phase API for the column-sharded mode (mused_b200/sharded.py drives it; the two
+// exchange points of SURVEY 8(e) sit between the phases):
+//   stage rows (<= room) -> [allreduce norm2] -> chunk_gram -> [allreduce G] -> chunk_finish
+//   get_begin -> [allreduce query Gram] -> get_finish
+long long bengine_room(BEngine* E);                       // rows the open chunk still takes
+int bengine_pending(BEngine* E);
+int bengine_ell(BEngine* E);                          // rows staged in the open chunk
+int bengine_stage(BEngine* E, const void* rows, long long m, long long ld, int dtype, int where, cudaStream_t st);
+int bengine_chunk_gram(BEngine* E, cudaStream_t st);     // K5 + K2 + split-K reduction into G (f64)
+int bengine_chunk_finish(BEngine* E, cudaStream_t st);   // K3 + K4
+// device buffers the collectives run on: norm2 [ell] f64, G [S][n2][n2] f64, query Gram [lda][lda] f64
+int bengine_buffers(BEngine* E, double** norm2, double** G, long long* g_count, double** QG, long long* qg_count);
+int bengine_get_begin(BEngine* E, int* level, int* ng, cudaStream_t st);   // open chunk must be closed
+int bengine_get_finish(BEngine* E, double* sketch, double* sigma2, double* vt, double* delta, int where,
+                       cudaStream_t st);
+
 // Shared query tail (swfd_engine.cu): top-l shrink of the float64 stack M (ng x d).
 struct QueryScratch {
     double *M = nullptr, *G = nullptr, *Vq = nullptr, *cs = nullptr, *eval = nullptr, *scr = nullptr;
     int *perm = nullptr, *counters = nullptr;
     int ng_max = 0, lda = 0;
+    double rel_thr = 0.1 * 2.220446049250313e-16;   // off-diagonal cut-off relative to mean |diag|
 };
+int merge_query_gram(const QueryScratch& Q, int ng, long long d, int sm_count, cudaStream_t st);
+int merge_query_solve(const QueryScratch& Q, int ng, long long d, int ell, int sm_count, double* o_sketch,
+                      double* o_vt, double* o_s2, cudaStream_t st);
 int merge_query(const QueryScratch& Q, int ng, long long d, int ell, int sm_count, double* o_sketch,
                 double* o_vt, double* o_s2, cudaStream_t st);
 

@@ -40,8 +40,8 @@ struct BSlot {                               // one FD instance of the batched e
 
 struct EigArgs {
     BSlot* slots;
-    const float* Gp;         // [S][KS][n2][n2] split-K partial Grams
-    int KS, ell, n2, capn;
+    const double* G;         // [S][n2][n2] Gram (split-K partials already added, all column shards)
+    int ell, n2, capn;
     const unsigned char* mask;  // [S][ell] 1 = row of the chunk is NOT part of this instance's batch
     int n_rows;              // rows in the chunk
     unsigned long long t_end;
@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
     double col[8][EPL];
     double nrm[8];
     {
-        const float* G0 = A.Gp + (size_t)s * A.KS * N2 * N2;
+        const double* G = A.G + (size_t)s * N2 * N2;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             const int j = 8 * w + k;
@@ -297,12 +297,7 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
             for (int e = 0; e < EPL; ++e) {
                 const int i = lane + 32 * e;
                 double v = 0.0;
-                if (!dj && !dead(i)) {
-                    for (int q = 0; q < A.KS; ++q) {
-                        const float* G = G0 + (size_t)q * N2 * N2;
-                        v += (double)G[(size_t)j * N2 + i] + (double)G[(size_t)i * N2 + j];
-                    }
-                }
+                if (!dj && !dead(i)) v = G[(size_t)j * N2 + i] + G[(size_t)i * N2 + j];
                 col[k][e] = 0.5 * v;
             }
         }

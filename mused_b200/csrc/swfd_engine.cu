@@ -107,7 +107,8 @@ __device__ __forceinline__ void rr_pair(int n, int r, int k, int& p, int& q) {
 // start; on exit diag(A) holds the eigenvalues and column i of V the vectors.
 // Cooperative launch (grid-wide sync between the rotation and update phases).
 __global__ void __launch_bounds__(256) k_jacobi(double* A, double* V, int n, int lda, double* cs,
-                                                int max_sweeps, int* counters, double* scratch) {
+                                                int max_sweeps, int* counters, double* scratch,
+                                                double rel_thr) {
     cg::grid_group grid = cg::this_grid();
     const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
     const int gth = gridDim.x * blockDim.x;
@@ -130,7 +131,7 @@ __global__ void __launch_bounds__(256) k_jacobi(double* A, double* V, int n, int
         }
     }
     grid.sync();
-    const double thr = 0.1 * DBL_EPSILON * scratch[0] / (double)n;
+    const double thr = rel_thr * scratch[0] / (double)n;    // rotations below this are skipped
     for (int sweep = 0; sweep < max_sweeps; ++sweep) {
         for (int r = 0; r < n - 1; ++r) {
             for (int k = gtid; k < half; k += gth) {
@@ -258,14 +259,21 @@ __global__ void k_fd_out(Dev D, int s, double* sketch, double* sigma2, double* v
 
 // Shared tail of both engines' get(): M (ng x d, float64) -> Gram -> Jacobi ->
 // top-l rows shrunk by the (l+1)-th eigenvalue (sliding_windows_frequent_directions.py:160-171).
-int merge_query(const QueryScratch& Q, int ng, long long d, int ell, int sm_count, double* o_sketch,
-                double* o_vt, double* o_s2, cudaStream_t st) {
+int merge_query_gram(const QueryScratch& Q, int ng, long long d, int sm_count, cudaStream_t st) {
     const int nj = ng + (ng & 1);
     MUSED_REQUIRE(nj <= Q.ng_max, "internal: stack of %d rows exceeds scratch %d", nj, Q.ng_max);
     MUSED_CUDA(cudaMemsetAsync(Q.G, 0, (size_t)Q.lda * Q.lda * sizeof(double), st));
     const int tiles = (ng + GT - 1) / GT;
     k_gram_f64<<<std::min(tiles * tiles, 8 * sm_count), 256, 0, st>>>(Q.M, ng, d, Q.G, Q.lda);
     MUSED_CUDA(cudaGetLastError());
+    COUNT_LAUNCH(1);
+    return 0;
+}
+
+// Column-sharded callers add the other ranks' Grams into Q.G between the two halves.
+int merge_query_solve(const QueryScratch& Q, int ng, long long d, int ell, int sm_count, double* o_sketch,
+                      double* o_vt, double* o_s2, cudaStream_t st) {
+    const int nj = ng + (ng & 1);
     MUSED_CUDA(cudaMemsetAsync(Q.counters, 0, 64 * sizeof(int), st));
     {
         int nb = 0;
@@ -279,7 +287,8 @@ int merge_query(const QueryScratch& Q, int ng, long long d, int ell, int sm_coun
         double *A_ = Q.G, *V_ = Q.Vq, *cs_ = Q.cs, *scr_ = Q.scr;
         int n_ = nj, lda_ = Q.lda, sweeps_ = 40;
         int* cnt_ = Q.counters;
-        void* args[] = {&A_, &V_, &n_, &lda_, &cs_, &sweeps_, &cnt_, &scr_};
+        double thr_ = Q.rel_thr;
+        void* args[] = {&A_, &V_, &n_, &lda_, &cs_, &sweeps_, &cnt_, &scr_, &thr_};
         MUSED_CUDA(cudaLaunchCooperativeKernel((void*)k_jacobi, dim3(grid), dim3(256), args, 0, st));
     }
     k_sort_eigs<<<(nj + 255) / 256, 256, 0, st>>>(Q.G, nj, Q.lda, Q.perm, Q.eval);
@@ -288,8 +297,15 @@ int merge_query(const QueryScratch& Q, int ng, long long d, int ell, int sm_coun
     k_merge_out<<<std::min(tm * tn, 8 * sm_count), 256, 0, st>>>(Q.M, ng, d, Q.Vq, Q.lda, Q.perm, Q.eval, ell,
                                                                   o_sketch, o_vt, o_s2);
     MUSED_CUDA(cudaGetLastError());
-    COUNT_LAUNCH(4);
+    COUNT_LAUNCH(3);
     return 0;
+}
+
+int merge_query(const QueryScratch& Q, int ng, long long d, int ell, int sm_count, double* o_sketch,
+                double* o_vt, double* o_s2, cudaStream_t st) {
+    int rc = merge_query_gram(Q, ng, d, sm_count, st);
+    if (rc) return rc;
+    return merge_query_solve(Q, ng, d, ell, sm_count, o_sketch, o_vt, o_s2, st);
 }
 
 // ---------------------------------------------------------------------------
@@ -718,6 +734,53 @@ int mused_swfd_kernel_ms(mused_swfd_t* h, int enable, double* ms5, int64_t* chun
     if (rows) *rows = r;
     return rc;
 }
+// ---- phase API of the column-sharded mode (batched schedule only) -----------------
+#define NEED_B(h) MUSED_REQUIRE((h) && (h)->B, "this call needs a schedule=batched handle")
+int mused_swfd_chunk_room(mused_swfd_t* h, int64_t* room, int64_t* pending) {
+    NEED_B(h);
+    if (room) *room = bengine_room(h->B);
+    if (pending) *pending = bengine_pending(h->B);
+    return 0;
+}
+int mused_swfd_stage(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld, int dtype, int where,
+                     void* stream) {
+    NEED_B(h);
+    return bengine_stage(h->B, rows, n_rows, ld, dtype, where, (cudaStream_t)stream);
+}
+int mused_swfd_chunk_gram(mused_swfd_t* h, void* stream) {
+    NEED_B(h);
+    return bengine_chunk_gram(h->B, (cudaStream_t)stream);
+}
+int mused_swfd_chunk_finish(mused_swfd_t* h, void* stream) {
+    NEED_B(h);
+    return bengine_chunk_finish(h->B, (cudaStream_t)stream);
+}
+int mused_swfd_exchange_buffers(mused_swfd_t* h, double** norm2, int64_t* norm2_count, double** gram,
+                                int64_t* gram_count, double** query_gram, int64_t* query_gram_count) {
+    NEED_B(h);
+    long long gc = 0, qc = 0;
+    int rc = bengine_buffers(h->B, norm2, gram, &gc, query_gram, &qc);
+    if (norm2_count) *norm2_count = bengine_ell(h->B);
+    if (gram_count) *gram_count = gc;
+    if (query_gram_count) *query_gram_count = qc;
+    return rc;
+}
+int mused_swfd_get_begin(mused_swfd_t* h, int32_t* level, int32_t* n_stack, void* stream) {
+    NEED_B(h);
+    int lv = 0, ng = 0;
+    int rc = bengine_get_begin(h->B, &lv, &ng, (cudaStream_t)stream);
+    if (level) *level = lv;
+    if (n_stack) *n_stack = ng;
+    return rc;
+}
+int mused_swfd_get_finish(mused_swfd_t* h, double* sketch, double* sigma2, double* vt, double* delta,
+                          int where, void* stream) {
+    NEED_B(h);
+    MUSED_REQUIRE(sketch && sigma2, "NULL argument");
+    return bengine_get_finish(h->B, sketch, sigma2, vt, delta, where, (cudaStream_t)stream);
+}
+#undef NEED_B
+
 int mused_swfd_queue_capacity(mused_swfd_t* h, int64_t* q) {
     MUSED_REQUIRE(h && q, "NULL argument");
     *q = h->B ? bengine_qcap(h->B) : h->E->D.capn;
