@@ -353,7 +353,7 @@ def run_ours(args, rank, local_rank, world):
         dur_s = km[dom] / chunks * 1e-3
         achieved = bytes_per_row * rows_per_launch / dur_s / 1e9
         roofline = {"bound": "hbm", "kernel": {"K1_stage": "k_bstage", "K5_book": "k_bbook", "K2_gram": "k_gram_tc",
-                                                "K3_eig": "k_eig_jacobi", "K4_rotate": "k_brotate"}[dom],
+                                                "K3_eig": "k_eig_jacobi", "K4_rotate": "k_rotate_tc"}[dom],
                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                     "peak_source": how, "algorithmic_bytes_per_row": bytes_per_row,
                     "rows_per_launch": rows_per_launch, "avg_launch_ms": km[dom] / chunks,
@@ -372,8 +372,10 @@ def run_ours(args, rank, local_rank, world):
                         "peak_bf16_TFLOPs": tpeak, "note": "kind::tf32 runs at half the bf16 rate; 3 passes"},
             "K3_eig": {"us_per_chunk": us["K3_eig"], "bound": "fp64-issue/barrier",
                        "share_of_step": km["K3_eig"] / main_res["ms_total"]},
-            "K4_rotate": {"us_per_chunk": us["K4_rotate"], "bound": "fp32 SIMT",
-                          "achieved_TFLOPs": S * 2.0 * ELL * n2 * D / (us["K4_rotate"] * 1e-6) / 1e12},
+            "K4_rotate": {"us_per_chunk": us["K4_rotate"], "bound": "tensor",
+                          "achieved_TFLOPs_dense": S * 2.0 * ELL * n2 * D / (us["K4_rotate"] * 1e-6) / 1e12,
+                          "issued_TFLOPs_3xTF32": 3 * S * 2.0 * ELL * n2 * D / (us["K4_rotate"] * 1e-6) / 1e12,
+                          "peak_bf16_TFLOPs": tpeak},
             "K5_book": {"us_per_chunk": us["K5_book"]},
         }
     elif main_res.get("k_launches"):

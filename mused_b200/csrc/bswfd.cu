@@ -4,7 +4,7 @@
 //   K5  k_bbook     period swap, snapshot expiry / cap trim, raw-row snapshots, masks
 //   K2  k_gram_tc   G = [sketch; chunk][sketch; chunk]^T          (tcgen05, gram_tc.cuh)
 //   K3  k_eig_jacobi  eig(G), shrink, dump decisions                (eig_jacobi.cuh)
-//   K4  k_brotate   sketch' = T [sketch; chunk], dumped rows -> snapshot ring
+//   K4  k_rotate_tc sketch' = T [sketch; chunk] (tcgen05, rotate_tc.cuh), dumped rows -> snapshot ring
 // with no host synchronisation between chunks.  The schedule and its arithmetic
 // are stated in oracle/swfd_batched_oracle.py; reference lines:
 //   swfd/seq_based_swfd.py:47-103, swfd/sliding_windows_frequent_directions.py:56-173,
@@ -15,6 +15,7 @@
 
 #include "bswfd.h"
 #include "gram_tc.cuh"
+#include "rotate_tc.cuh"
 
 namespace mused {
 
@@ -143,86 +144,6 @@ __global__ void __launch_bounds__(256) k_gram_reduce(BDev D) {
 }
 
 // ---------------------------------------------------------------------------
-// K4: shrink + rotate (frequent_directions.py:86-93, :58):
-//   out[r][c] = sum_k T[r][k] * R[k][c],  R = [sketch(src plane); chunk]
-// 64 x 64 output tile per CTA, fp32 FMA on the exact hi + lo values.  Rows whose
-// direction is dumped (fastfdwithdump.py:115-131) go to their snapshot-ring
-// entry instead and leave a zero row in the sketch.
-// ---------------------------------------------------------------------------
-constexpr int RT = 64, RK = 16;
-__global__ void __launch_bounds__(256) k_brotate(BDev D) {
-    __shared__ float sa[RK][RT + 4];
-    __shared__ float sb[RK][RT + 4];
-    const int s = blockIdx.z;
-    const BSlot& sl = D.slots[s];
-    if (sl.skip) return;
-    const int ell = D.ell, n2 = D.n2;
-    const long long d = D.d;
-    const int r0 = blockIdx.y * RT;
-    const long long c0 = (long long)blockIdx.x * RT;
-    const int src = sl.src;
-    const float* Ts = D.T + (size_t)s * ell * n2;
-    const float* skh = D.skhi + ((size_t)s * 2 + src) * ell * d;
-    const float* skl = D.sklo + ((size_t)s * 2 + src) * ell * d;
-    const int t = threadIdx.x, ty = t >> 4, tx = t & 15;
-    float acc[4][4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-    for (int k0 = 0; k0 < n2; k0 += RK) {
-#pragma unroll
-        for (int e = t; e < RT * RK; e += 256) {
-            const int kk = e & (RK - 1), mm = e >> 4;          // T: k contiguous
-            const int r = r0 + mm;
-            sa[kk][mm] = (r < ell) ? Ts[(size_t)r * n2 + k0 + kk] : 0.f;
-            const int nn = e & (RT - 1), kb = e >> 6;          // R: c contiguous
-            const int k = k0 + kb;
-            const long long c = c0 + nn;
-            float v = 0.f;
-            if (c < d) {
-                if (k < ell) v = skh[(size_t)k * d + c] + skl[(size_t)k * d + c];
-                else v = D.xhi[(size_t)(k - ell) * d + c] + D.xlo[(size_t)(k - ell) * d + c];
-            }
-            sb[kb][nn] = v;
-        }
-        __syncthreads();
-#pragma unroll
-        for (int kk = 0; kk < RK; ++kk) {
-            float av[4], bv[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) av[i] = sa[kk][ty * 4 + i];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) bv[j] = sb[kk][tx * 4 + j];
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
-        }
-        __syncthreads();
-    }
-    float* dh = D.skhi + ((size_t)s * 2 + (src ^ 1)) * ell * d;
-    float* dl = D.sklo + ((size_t)s * 2 + (src ^ 1)) * ell * d;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int r = r0 + ty * 4 + i;
-        if (r >= ell) continue;
-        const int ds = D.dump_slot[(size_t)s * ell + r];
-        float* ring = ds >= 0 ? D.ringV + ((size_t)s * D.capn + ds) * d : nullptr;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const long long c = c0 + tx * 4 + j;
-            if (c >= d) continue;
-            float h = 0.f, l = 0.f;
-            if (ring) ring[c] = acc[i][j];
-            else umma::split_tf32(acc[i][j], h, l);
-            dh[(size_t)r * d + c] = h;
-            dl[(size_t)r * d + c] = l;
-        }
-    }
-}
-
-// ---------------------------------------------------------------------------
 // Query support: float64 stack [sketch; live snapshots] of one instance, and the
 // plain FD output (sketch, sigma^2, Vt = sketch / sqrt(sigma^2), delta).
 // ---------------------------------------------------------------------------
@@ -271,7 +192,8 @@ struct BEngine {
     unsigned long long time = 0;      // rows handed to fit()
     unsigned long long done = 0;      // rows folded into the state
     int pend = 0;                     // rows staged in the chunk planes, not yet processed
-    CUtensorMap tm_sk_hi, tm_sk_lo, tm_x_hi, tm_x_lo;
+    CUtensorMap tm_sk_hi, tm_sk_lo, tm_x_hi, tm_x_lo;                 // K2 boxes: l rows x 32 columns
+    CUtensorMap tr_t_hi, tr_t_lo, tr_sk_hi, tr_sk_lo, tr_x_hi, tr_x_lo; // K4 boxes
     unsigned char* raw = nullptr;     // H2D staging of caller rows
     size_t raw_bytes = 0;
     QueryScratch Q;
@@ -372,7 +294,8 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     A_(D.mask, Sa * ell);
     A_(D.Gp, Sa * KS * D.n2 * D.n2);
     A_(D.G, Sa * D.n2 * D.n2);
-    A_(D.T, Sa * ell * D.n2);
+    A_(D.Thi, Sa * ell * D.n2 + 128 * D.n2);   // + slack: the 128-row T box of the last instance
+    A_(D.Tlo, Sa * ell * D.n2 + 128 * D.n2);
     A_(D.s2, Sa * ell);
     A_(D.dump_slot, Sa * ell);
     A_(D.ringV, Sa * D.capn * d);
@@ -411,6 +334,18 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     CUresult r2 = encode_tmap_f32_2d(&E->tm_sk_lo, D.sklo, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
     CUresult r3 = encode_tmap_f32_2d(&E->tm_x_hi, D.xhi, (uint64_t)ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
     CUresult r4 = encode_tmap_f32_2d(&E->tm_x_lo, D.xlo, (uint64_t)ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
+    {
+        const uint32_t trows = (uint32_t)std::min<long long>(ell, 128), brows = (uint32_t)std::min<long long>(ell, 32);
+        CUresult q[6];
+        q[0] = encode_tmap_f32_2d(&E->tr_t_hi, D.Thi, (uint64_t)Sa * ell, (uint64_t)D.n2, (uint64_t)D.n2, trows);
+        q[1] = encode_tmap_f32_2d(&E->tr_t_lo, D.Tlo, (uint64_t)Sa * ell, (uint64_t)D.n2, (uint64_t)D.n2, trows);
+        q[2] = encode_tmap_f32_2d(&E->tr_sk_hi, D.skhi, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, brows, 32, true);
+        q[3] = encode_tmap_f32_2d(&E->tr_sk_lo, D.sklo, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, brows, 32, true);
+        q[4] = encode_tmap_f32_2d(&E->tr_x_hi, D.xhi, (uint64_t)ell, (uint64_t)d, (uint64_t)d, brows, 32, true);
+        q[5] = encode_tmap_f32_2d(&E->tr_x_lo, D.xlo, (uint64_t)ell, (uint64_t)d, (uint64_t)d, brows, 32, true);
+        for (int i = 0; i < 6; ++i)
+            if (q[i] != CUDA_SUCCESS) r1 = q[i];
+    }
     if (r1 != CUDA_SUCCESS || r2 != CUDA_SUCCESS || r3 != CUDA_SUCCESS || r4 != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled failed (%d %d %d %d)", (int)r1, (int)r2, (int)r3, (int)r4);
         delete E;
@@ -462,7 +397,8 @@ static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t 
     A.mask = E.D.mask;
     A.n_rows = n;
     A.t_end = t_end;
-    A.T = E.D.T;
+    A.Thi = E.D.Thi;
+    A.Tlo = E.D.Tlo;
     A.s2 = E.D.s2;
     A.dump_slot = E.D.dump_slot;
     A.ringS = E.D.ringS;
@@ -532,7 +468,13 @@ int bengine_chunk_finish(BEngine* Ep, cudaStream_t st) {
         if (rc) return rc;
         E.mark(3, st);
         E.mark(4, st);
-        k_brotate<<<dim3((unsigned)((D.d + RT - 1) / RT), (unsigned)((D.ell + RT - 1) / RT), (unsigned)D.S), 256, 0, st>>>(D);
+        static bool rot_attr = false;
+        if (!rot_attr) {
+            MUSED_CUDA(cudaFuncSetAttribute(k_rotate_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, RotCfg::SMEM_BYTES));
+            rot_attr = true;
+        }
+        k_rotate_tc<<<dim3((unsigned)((D.d + RotCfg::NT - 1) / RotCfg::NT), (unsigned)D.S), 192, RotCfg::SMEM_BYTES, st>>>(
+            E.tr_t_hi, E.tr_t_lo, E.tr_sk_hi, E.tr_sk_lo, E.tr_x_hi, E.tr_x_lo, D);
         MUSED_CUDA(cudaGetLastError());
         E.mark(4, st);
         mused_count_launches(2);

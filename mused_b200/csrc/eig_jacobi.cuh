@@ -45,7 +45,7 @@ struct EigArgs {
     const unsigned char* mask;  // [S][ell] 1 = row of the chunk is NOT part of this instance's batch
     int n_rows;              // rows in the chunk
     unsigned long long t_end;
-    float* T;                // [S][ell][n2] rotate coefficients
+    float *Thi, *Tlo;        // [S][ell][n2] rotate coefficients, TF32 hi / lo planes
     double* s2;              // [S][ell]
     int* dump_slot;          // [S][ell] ring entry or -1
     unsigned long long* ringS;  // [S][capn]
@@ -393,7 +393,8 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
 
     // ---- outputs -------------------------------------------------------------------------
     const int src_plane = sl.cur;
-    float* Ts = A.T + (size_t)s * ELL * N2;
+    float* Th = A.Thi + (size_t)s * ELL * N2;
+    float* Tl = A.Tlo + (size_t)s * ELL * N2;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
         const int r = rk[k];
@@ -402,7 +403,15 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
         const double s2v = fmax(lam - cut, 0.0);
         const double coef = (lam > 0.0 && s2v > 0.0) ? sqrt(s2v / lam) / lam : 0.0;
 #pragma unroll
-        for (int e = 0; e < EPL; ++e) Ts[(size_t)r * N2 + lane + 32 * e] = (float)(coef * col[k][e]);
+        for (int e = 0; e < EPL; ++e) {
+            const float v = (float)(coef * col[k][e]);
+            uint32_t hb, lb;
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hb) : "f"(v));
+            const float hi = __uint_as_float(hb);
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lb) : "f"(v - hi));
+            Th[(size_t)r * N2 + lane + 32 * e] = hi;
+            Tl[(size_t)r * N2 + lane + 32 * e] = __uint_as_float(lb);
+        }
         if (lane == 0) {
             const bool dumped = s2v >= thr;
             int slot = -1;

@@ -121,18 +121,21 @@ __device__ __forceinline__ uint64_t smem_desc_k_sw128(uint32_t smem_addr) {
     d |= (uint64_t)2 << 61;
     return d;
 }
-// Same swizzle, MN-major operand: rows of 128 bytes hold 32 consecutive M/N
-// elements of one k; 8 k-rows form a 1024-byte atom.  `mn_atom_stride_bytes` is
-// the distance between atoms that follow each other along M/N (LBO) and
-// `k_atom_stride_bytes` between atoms along K (SBO).
-__device__ __forceinline__ uint64_t smem_desc_mn_sw128(uint32_t smem_addr, uint32_t mn_atom_stride_bytes,
-                                                       uint32_t k_atom_stride_bytes) {
+// MN-major operand of 32-bit elements.  The only layout the tensor core accepts for
+// MN-major TF32 is SWIZZLE_128B_BASE32B (cutlass sm100_common.inl: "for mn-major
+// tf32 operands, SW128_32B is the only available smem layout"): rows of 128 bytes
+// hold 32 consecutive M/N elements of one k, FOUR k-rows form one 512-byte swizzle
+// atom in which the 32-byte chunk index is XORed with the row index (what TMA's
+// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B writes).  `mn_atom_stride_bytes` = distance
+// between atoms along M/N (LBO), `k_atom_stride_bytes` between atoms along K (SBO).
+__device__ __forceinline__ uint64_t smem_desc_mn_sw128_32b(uint32_t smem_addr, uint32_t mn_atom_stride_bytes,
+                                                           uint32_t k_atom_stride_bytes) {
     uint64_t d = 0;
     d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
     d |= (uint64_t)((mn_atom_stride_bytes >> 4) & 0x3FFF) << 16;
     d |= (uint64_t)((k_atom_stride_bytes >> 4) & 0x3FFF) << 32;
     d |= (uint64_t)1 << 46;
-    d |= (uint64_t)2 << 61;
+    d |= (uint64_t)1 << 61;          // LayoutType::SWIZZLE_128B_BASE32B
     return d;
 }
 // Instruction descriptor (InstrDescriptor, same header): D=F32 [4,6)=1, A/B=TF32
@@ -143,11 +146,20 @@ __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N, int a_mn_major, 
            ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
-// hi/lo split of an fp32 value for the 3xTF32 product: hi keeps the 10 mantissa
-// bits a TF32 operand carries, lo = v - hi is exact in fp32.
+// hi/lo split of an fp32 value for the 3xTF32 product.  Both parts are rounded to
+// nearest TF32 (cvt.rna): the tensor core TRUNCATES the low 13 bits of an operand,
+// and a truncated lo part biases every product towards zero by ~2^-22 -- harmless in
+// the Gram (a measurement) but a systematic shrink of the sketch when it accumulates
+// through the rotate chunk after chunk.  Pre-rounded parts pass the truncation
+// unchanged; hi + lo reproduces v to 2^-23 relative, unbiased.
+__device__ __forceinline__ float rna_tf32(float v) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return __uint_as_float(r);
+}
 __device__ __forceinline__ void split_tf32(float v, float& hi, float& lo) {
-    hi = __uint_as_float(__float_as_uint(v) & 0xFFFFE000u);
-    lo = v - hi;
+    hi = rna_tf32(v);
+    lo = rna_tf32(v - hi);
 }
 
 }  // namespace umma
@@ -156,7 +168,8 @@ __device__ __forceinline__ void split_tf32(float v, float& hi, float& lo) {
 // (no link-time dependency on libcuda).  2-D fp32 row-major tensor
 // [rows][cols], box = box_rows x 32 floats, SWIZZLE_128B.
 inline CUresult encode_tmap_f32_2d(CUtensorMap* out, const float* base, uint64_t rows, uint64_t cols,
-                                   uint64_t ld_elems, uint32_t box_rows, uint32_t box_cols = 32) {
+                                   uint64_t ld_elems, uint32_t box_rows, uint32_t box_cols = 32,
+                                   bool atom32b = false) {
     typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -173,7 +186,9 @@ inline CUresult encode_tmap_f32_2d(CUtensorMap* out, const float* base, uint64_t
     cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
     return fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, gdim, gstr, box, estr,
-              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+              CU_TENSOR_MAP_INTERLEAVE_NONE,
+              atom32b ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+              CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 }
 

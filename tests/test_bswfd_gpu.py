@@ -7,8 +7,11 @@ Bars: identical schedule (snapshot (s, t) stamps, flush / dump / raw counts, cho
 level, get_size); singular values within 1e-4 relative for sigma >= 0.05 sigma_max
 and 1e-5 sigma_max absolute below (the Gram route carries fp32 products: an
 eigenvalue is known to ~1e-6 lambda_max absolute, so sigma_i to 5e-7 (sigma_max /
-sigma_i)^2 relative); covariance error within 1e-3 relative (north_star) -- the
-asserted bounds are 20x tighter than north_star's."""
+sigma_i)^2 relative); covariance error within 1e-3 relative (north_star).  The
+asserted bounds are 5x / 10x tighter than north_star's: the 3xTF32 rotate on the
+tensor cores accumulates with truncation, which shows as a systematic ~2e-8 relative
+shrink of the sketch per chunk (measured 2.5e-6 .. 6e-6 on sigma after 30 .. 150
+chunks; an FD instance lives 2N rows)."""
 import numpy as np
 import pytest
 import torch
@@ -19,8 +22,8 @@ from oracle.swfd_batched_oracle import BatchedSeqSWFD
 
 pytestmark = pytest.mark.gpu
 
-SIG_RTOL = 5e-6      # north_star: 1e-4
-COV_RTOL = 5e-5      # north_star: 1e-3
+SIG_RTOL = 2e-5      # north_star: 1e-4
+COV_RTOL = 1e-4      # north_star: 1e-3
 
 
 def _check_query(gpu, ora, Aw):
@@ -41,8 +44,8 @@ def _check_query(gpu, ora, Aw):
         assert g["q_s"] == o["q_s"] and g["q_t"] == o["q_t"]
         assert (g["n_flush"], g["n_dump"], g["n_raw"]) == (o["n_flush"], o["n_dump"], o["n_raw"])
         assert g["last_dump_time"] == o["last_dump_time"]
-        assert abs(g["delta"] - o["delta"]) <= 1e-5 * o["delta"] + 1e-12
-        np.testing.assert_allclose(np.sort(g["s2"]), np.sort(o["s2"]), atol=2e-5 * max(o["s2"].max(), 1e-30))
+        assert abs(g["delta"] - o["delta"]) <= 1e-4 * o["delta"] + 1e-12
+        np.testing.assert_allclose(np.sort(g["s2"]), np.sort(o["s2"]), atol=5e-5 * max(o["s2"].max(), 1e-30))
     return eg, eo
 
 
