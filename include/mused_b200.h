@@ -208,6 +208,18 @@ int mused_topk_adjacency(const float* feats, int64_t W, int64_t f, int64_t ld, i
 int mused_contingency(const int32_t* prev, const int32_t* cur, int64_t n, int32_t P,
                       int32_t Q, int32_t* counts, void* stream);
 
+/* Symmetric eigen-decomposition of a positive semi-definite Gram matrix
+ * (what replaces scipy.linalg.svd(..., lapack_driver="gesvd") of the stacked
+ * rows in SlidingWindowFD.get, sliding_windows_frequent_directions.py:160, and
+ * the query of SeqBasedSWFD.get, seq_based_swfd.py:83-100: singular values =
+ * sqrt(evals), left singular vectors = vecs).  G: n x n float64 device, leading
+ * dimension ld; evals (n, descending) and vecs (n x n, ROW i = eigenvector i,
+ * leading dimension ld_vecs) are device buffers.  Whole-GPU one-sided block
+ * Jacobi (csrc/eig_big.cuh); n up to ~1750 on a 148-SM B200.  Synchronises
+ * the stream.  *sweeps (nullable) = Jacobi sweeps taken. */
+int mused_sym_eig(const double* G, int64_t n, int64_t ld, double* evals, double* vecs,
+                  int64_t ld_vecs, int32_t* sweeps, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -44,7 +44,7 @@ SYMBOLS = [
     "mused_swfd_exchange_buffers", "mused_swfd_get_begin", "mused_swfd_get_finish",
     "mused_fd_create", "mused_fd_destroy", "mused_fd_fit", "mused_fd_fit_batches",
     "mused_fd_dump", "mused_fd_flush", "mused_fd_get",
-    "mused_assign", "mused_topk_adjacency", "mused_contingency",
+    "mused_assign", "mused_topk_adjacency", "mused_contingency", "mused_sym_eig",
 ]
 
 
@@ -91,6 +91,7 @@ def load():
     lib.mused_assign.argtypes = [vp, i64, i64, i64, vp, i64, i64, C.c_int, C.c_float, vp, vp, vp]
     lib.mused_topk_adjacency.argtypes = [vp, i64, i64, i64, C.c_int, i64, vp, vp]
     lib.mused_contingency.argtypes = [vp, vp, i64, i32, i32, vp, vp]
+    lib.mused_sym_eig.argtypes = [vp, i64, i64, vp, vp, i64, C.POINTER(i32), vp]
     _lib = lib
     return lib
 

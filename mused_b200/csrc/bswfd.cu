@@ -200,6 +200,7 @@ struct BEngine {
     double *o_sketch = nullptr, *o_vt = nullptr, *o_s2 = nullptr, *o_delta = nullptr;
     std::vector<void*> allocs;
     int q_slot = 0, q_ng = 0;         // pending query (get_begin -> get_finish)
+    bool q_gram = true;               // get_begin left the stack Gram in Q.G
     bool timing = false;
     std::vector<cudaEvent_t> ev[5];
     double timed_ms[5] = {0, 0, 0, 0, 0};
@@ -312,8 +313,14 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     A_(Q.G, (size_t)Q.lda * Q.lda);
     A_(Q.Vq, (size_t)Q.lda * Q.lda);
     A_(Q.cs, (size_t)Q.ng_max);
-    A_(Q.eval, (size_t)Q.ng_max);
-    A_(Q.perm, (size_t)Q.ng_max);
+    Q.plan_big();
+    A_(Q.eval, (size_t)Q.npad_max);
+    A_(Q.perm, (size_t)Q.npad_max);
+    A_(Q.lam, (size_t)Q.npad_max);
+    A_(Q.VT, (size_t)Q.npad_max * Q.ldt);
+    A_(Q.mailL, Q.mail_count);
+    A_(Q.mailR, Q.mail_count);
+    A_(Q.sync, (size_t)QSYNC_WORDS);
     A_(Q.counters, 64);
     A_(Q.scr, 8);
     A_(E->o_sketch, (size_t)ell * d);
@@ -595,7 +602,7 @@ static int b_copy_out(double* dst, const double* src, size_t n, int where, cudaS
 // SeqBasedSWFD.get, first half: level choice (seq_based_swfd.py:83-98), stack
 // [C; snapshots] of the chosen level and its float64 Gram.  *ng = rows of the
 // stack, 0 when the level has no snapshots (no Gram needed).
-int bengine_get_begin(BEngine* Ep, int* level, int* ng_out, cudaStream_t st) {
+static int b_get_begin(BEngine* Ep, int* level, int* ng_out, bool with_gram, cudaStream_t st) {
     BEngine& E = *Ep;
     BDev& D = E.D;
     if (E.n_levels == 0) {
@@ -627,11 +634,16 @@ int bengine_get_begin(BEngine* Ep, int* level, int* ng_out, cudaStream_t st) {
         k_bgather<<<std::min(ng, 4 * E.sm_count), 256, 0, st>>>(D, s, E.Q.M);
         MUSED_CUDA(cudaGetLastError());
         mused_count_launches(1);
-        if ((rc = merge_query_gram(E.Q, ng, D.d, E.sm_count, st))) return rc;
+        if (with_gram && (rc = merge_query_gram(E.Q, ng, D.d, E.sm_count, st))) return rc;
+        E.q_gram = with_gram;
         E.q_ng = ng;
     }
     if (ng_out) *ng_out = E.q_ng;
     return 0;
+}
+
+int bengine_get_begin(BEngine* Ep, int* level, int* ng_out, cudaStream_t st) {
+    return b_get_begin(Ep, level, ng_out, true, st);
 }
 
 int bengine_get_finish(BEngine* Ep, double* sketch, double* sigma2, double* vt, double* delta, int where,
@@ -646,7 +658,10 @@ int bengine_get_finish(BEngine* Ep, double* sketch, double* sigma2, double* vt, 
         MUSED_CUDA(cudaGetLastError());
         mused_count_launches(1);
     } else {
-        if ((rc = merge_query_solve(E.Q, E.q_ng, D.d, D.ell, E.sm_count, E.o_sketch, vt ? E.o_vt : nullptr, E.o_s2, st))) return rc;
+        // single-GPU get(): Gram or covariance side, whichever is smaller; phase API: the Gram is in Q.G
+        if (E.q_gram) rc = merge_query_solve(E.Q, E.q_ng, D.d, D.ell, E.sm_count, E.o_sketch, vt ? E.o_vt : nullptr, E.o_s2, st);
+        else rc = merge_query(E.Q, E.q_ng, D.d, D.ell, E.sm_count, E.o_sketch, vt ? E.o_vt : nullptr, E.o_s2, st);
+        if (rc) return rc;
         MUSED_CUDA(cudaMemsetAsync(E.o_delta, 0, sizeof(double), st));
     }
     if ((rc = b_copy_out(sketch, E.o_sketch, ld_out, where, st))) return rc;
@@ -668,7 +683,7 @@ int bengine_get(BEngine* Ep, double* sketch, double* sigma2, double* vt, double*
     int rc = process_chunk(E, st);      // get() closes the open chunk (the reference flushes on get, too)
     if (rc) return rc;
     int ng = 0;
-    if ((rc = bengine_get_begin(Ep, level, &ng, st))) return rc;
+    if ((rc = b_get_begin(Ep, level, &ng, false, st))) return rc;
     return bengine_get_finish(Ep, sketch, sigma2, vt, delta, where, st);
 }
 

@@ -67,7 +67,20 @@ struct QueryScratch {
     int *perm = nullptr, *counters = nullptr;
     int ng_max = 0, lda = 0;
     double rel_thr = 0.1 * 2.220446049250313e-16;   // off-diagonal cut-off relative to mean |diag|
+    // whole-GPU block Jacobi (eig_big.cuh): eigenvalues per column slot, eigenvectors one per row,
+    // neighbour mailboxes, flags / reductions / info (zeroed per call)
+    double *lam = nullptr, *VT = nullptr, *mailL = nullptr, *mailR = nullptr;
+    unsigned long long* sync = nullptr;
+    int npad_max = 0, ldt = 0;
+    size_t mail_count = 0;
+    double big_tol = 1e-4;                           // largest cosine measured in the last sweep
+    void plan_big() {
+        npad_max = ng_max + 12;
+        ldt = (ng_max + 31) / 32 * 32;
+        mail_count = (size_t)(ng_max / 2 + 8) * ldt;
+    }
 };
+constexpr int QSYNC_WORDS = 1024;   // flagL[256] | flagR[256] | red[128] | info
 int merge_query_gram(const QueryScratch& Q, int ng, long long d, int sm_count, cudaStream_t st);
 int merge_query_solve(const QueryScratch& Q, int ng, long long d, int ell, int sm_count, double* o_sketch,
                       double* o_vt, double* o_s2, cudaStream_t st);

@@ -8,6 +8,7 @@
 
 #include "swfd_device.cuh"
 #include "bswfd.h"
+#include "eig_big.cuh"
 
 namespace mused {
 
@@ -205,6 +206,7 @@ __global__ void k_sort_eigs(const double* A, int n, int lda, int* perm, double* 
 
 // sketch[i] = sqrt(s_i) * vt[i],  vt[i] = (1/sqrt(lam_i)) sum_j V[j][perm[i]] M[j],
 // s_i = lam_i - lam_l (when ng > l).  One 64x64 tile per CTA.
+template <bool VT_LAYOUT>   // VT_LAYOUT: eigenvector i is ROW perm[i] of V (eig_big.cuh); else column perm[i]
 __global__ void __launch_bounds__(256) k_merge_out(const double* __restrict__ M, int ng, long long d,
                                                    const double* __restrict__ V, int lda,
                                                    const int* __restrict__ perm,
@@ -215,10 +217,11 @@ __global__ void __launch_bounds__(256) k_merge_out(const double* __restrict__ M,
     const int tm = (ell + GT - 1) / GT, tn = (int)((d + GT - 1) / GT);
     for (int tile = blockIdx.x; tile < tm * tn; tile += gridDim.x) {
         const int m0 = (tile / tn) * GT, n0 = (tile % tn) * GT;
-        gemm_tile_f64<false, true>(
+        gemm_tile_f64<VT_LAYOUT, true>(
             sm, threadIdx.x, m0, n0, ng,
             [&](int i, int j) -> double {
-                return (i < ell && i < ng && j < ng) ? V[(size_t)j * lda + perm[i]] : 0.0;
+                if (!(i < ell && i < ng && j < ng)) return 0.0;
+                return VT_LAYOUT ? V[(size_t)perm[i] * lda + j] : V[(size_t)j * lda + perm[i]];
             },
             [&](int j, int c) -> double { return (j < ng && c < d) ? M[(size_t)j * d + c] : 0.0; },
             [&](int i, int c, double v) {
@@ -257,6 +260,58 @@ __global__ void k_fd_out(Dev D, int s, double* sketch, double* sigma2, double* v
 }
 
 
+// C = M^T M (d x d, leading dimension lda), float64: the covariance side of the stack, used
+// when it has more rows than columns (its eigenvectors ARE the right singular vectors).
+__global__ void __launch_bounds__(256) k_cov_f64(const double* __restrict__ M, int ng, long long d,
+                                                 double* __restrict__ Cm, int lda) {
+    __shared__ GemmSmem sm;
+    const int tiles = (int)((d + GT - 1) / GT);
+    for (int tile = blockIdx.x; tile < tiles * tiles; tile += gridDim.x) {
+        const int ti = tile / tiles, tj = tile % tiles;
+        if (tj > ti) continue;
+        const int m0 = ti * GT, n0 = tj * GT;
+        gemm_tile_f64<false, true>(
+            sm, threadIdx.x, m0, n0, ng,
+            [&](int i, int r) -> double { return (i < d && r < ng) ? M[(size_t)r * d + i] : 0.0; },
+            [&](int r, int j) -> double { return (j < d && r < ng) ? M[(size_t)r * d + j] : 0.0; },
+            [&](int i, int j, double v) {
+                if (i < d && j < d) {
+                    Cm[(size_t)i * lda + j] = v;
+                    Cm[(size_t)j * lda + i] = v;
+                }
+            },
+            [&]() { __syncthreads(); });
+    }
+}
+
+// covariance-side output: vt[i] = eigenvector i (row perm[i] of VT), sketch[i] = sqrt(lam_i - lam_l) vt[i]
+__global__ void k_cov_out(const double* __restrict__ VT, int ldt, const int* __restrict__ perm,
+                          const double* __restrict__ eval, int n, int ell, long long d, double* sketch, double* vt,
+                          double* sigma2) {
+    const double cut = (n > ell) ? fmax(eval[ell], 0.0) : 0.0;
+    for (int i = blockIdx.x; i < ell; i += gridDim.x) {
+        const double li = (i < n) ? fmax(eval[i], 0.0) : 0.0;
+        const double sc = sqrt(fmax(li - cut, 0.0));
+        const double* src = VT + (size_t)perm[i < n ? i : 0] * ldt;
+        for (long long c = threadIdx.x; c < d; c += blockDim.x) {
+            const double v = (i < n && li > 0.0) ? src[c] : 0.0;
+            if (vt) vt[(size_t)i * d + c] = v;
+            sketch[(size_t)i * d + c] = v * sc;
+        }
+        if (threadIdx.x == 0) sigma2[i] = li - cut;
+    }
+}
+
+// rows of VT in descending eigenvalue order -> vecs (n x n, row i = eigenvector i)
+__global__ void k_eig_permute_out(const double* __restrict__ VT, int ldt, const int* __restrict__ perm,
+                                  const double* __restrict__ eval, int n, double* evals, double* vecs, long long ldv) {
+    for (int i = blockIdx.x; i < n; i += gridDim.x) {
+        const double* src = VT + (size_t)perm[i] * ldt;
+        for (int c = threadIdx.x; c < n; c += blockDim.x) vecs[(size_t)i * ldv + c] = src[c];
+        if (threadIdx.x == 0) evals[i] = eval[i];
+    }
+}
+
 // Shared tail of both engines' get(): M (ng x d, float64) -> Gram -> Jacobi ->
 // top-l rows shrunk by the (l+1)-th eigenvalue (sliding_windows_frequent_directions.py:160-171).
 int merge_query_gram(const QueryScratch& Q, int ng, long long d, int sm_count, cudaStream_t st) {
@@ -270,9 +325,86 @@ int merge_query_gram(const QueryScratch& Q, int ng, long long d, int sm_count, c
     return 0;
 }
 
+// Whole-GPU block Jacobi (eig_big.cuh) when the matrix fits the co-resident CTAs'
+// shared memory; *done = false -> the caller falls back to k_jacobi.
+template <int CB>
+static int launch_eig_big(const QueryScratch& Q, int n, int sm_count, cudaStream_t st, int* npad, bool* done) {
+    *done = false;
+    const int nr = (n + 31) / 32 * 32;
+    const int P = (n + 2 * CB - 1) / (2 * CB);
+    const size_t smem = big::Cfg<CB>::smem_bytes(nr);
+    if (smem > 227u * 1024u || P > sm_count || P > 256 || nr > Q.ldt || 2 * P * CB > Q.npad_max ||
+        (size_t)P * CB * nr > Q.mail_count)
+        return 0;
+    static bool attr_done = false;
+    if (!attr_done) {
+        MUSED_CUDA(cudaFuncSetAttribute(big::k_eig_big<CB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_done = true;
+    }
+    int nb = 0;
+    MUSED_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, big::k_eig_big<CB>, big::NT, smem));
+    if (nb < 1) return 0;
+    MUSED_CUDA(cudaMemsetAsync(Q.sync, 0, (size_t)QSYNC_WORDS * sizeof(unsigned long long), st));
+    big::Args a;
+    a.G = Q.G; a.lda = Q.lda; a.n = n; a.nr = nr; a.P = P;
+    a.mailL = Q.mailL; a.mailR = Q.mailR;
+    a.flagL = Q.sync; a.flagR = Q.sync + 256; a.red = Q.sync + 512;
+    a.lam = Q.lam; a.VT = Q.VT; a.ldt = Q.ldt;
+    a.tol = Q.big_tol; a.max_sweeps = 40;
+    a.info = reinterpret_cast<int*>(Q.sync + 640);
+    a.prof = Q.sync + 700;
+    void* args[] = {&a};
+    MUSED_CUDA(cudaLaunchCooperativeKernel((void*)big::k_eig_big<CB>, dim3(P), dim3(big::NT), args, smem, st));
+    *npad = 2 * P * CB;
+    *done = true;
+    return 0;
+}
+
+static int eig_big_cb_floor() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("MUSED_EIG_CB");
+        v = e ? atoi(e) : 4;
+        if (v < 1) v = 1;
+        if (v > 6) v = 6;
+    }
+    return v;
+}
+
+static int dispatch_eig_big(const QueryScratch& Q, int n, int sm_count, cudaStream_t st, int* npad, bool* done) {
+    *done = false;
+    int cb = (n + 2 * sm_count - 1) / (2 * sm_count);
+    if (cb < eig_big_cb_floor()) cb = eig_big_cb_floor();
+    switch (cb) {
+        case 1: return launch_eig_big<1>(Q, n, sm_count, st, npad, done);
+        case 2: return launch_eig_big<2>(Q, n, sm_count, st, npad, done);
+        case 3: return launch_eig_big<3>(Q, n, sm_count, st, npad, done);
+        case 4: return launch_eig_big<4>(Q, n, sm_count, st, npad, done);
+        case 5: return launch_eig_big<5>(Q, n, sm_count, st, npad, done);
+        case 6: return launch_eig_big<6>(Q, n, sm_count, st, npad, done);
+        default: return 0;
+    }
+}
+
 // Column-sharded callers add the other ranks' Grams into Q.G between the two halves.
 int merge_query_solve(const QueryScratch& Q, int ng, long long d, int ell, int sm_count, double* o_sketch,
                       double* o_vt, double* o_s2, cudaStream_t st) {
+    const int tm = (ell + GT - 1) / GT, tn = (int)((d + GT - 1) / GT);
+    bool big_done = false;
+    int npad = 0;
+    if (Q.VT && !getenv("MUSED_EIG_LEGACY")) {
+        int rc = dispatch_eig_big(Q, ng, sm_count, st, &npad, &big_done);
+        if (rc) return rc;
+    }
+    if (big_done) {
+        k_sort_eigs<<<(npad + 255) / 256, 256, 0, st>>>(Q.lam, npad, 0, Q.perm, Q.eval);
+        MUSED_CUDA(cudaGetLastError());
+        k_merge_out<true><<<std::min(tm * tn, 8 * sm_count), 256, 0, st>>>(Q.M, ng, d, Q.VT, Q.ldt, Q.perm, Q.eval, ell,
+                                                                          o_sketch, o_vt, o_s2);
+        MUSED_CUDA(cudaGetLastError());
+        COUNT_LAUNCH(3);
+        return 0;
+    }
     const int nj = ng + (ng & 1);
     MUSED_CUDA(cudaMemsetAsync(Q.counters, 0, 64 * sizeof(int), st));
     {
@@ -293,9 +425,8 @@ int merge_query_solve(const QueryScratch& Q, int ng, long long d, int ell, int s
     }
     k_sort_eigs<<<(nj + 255) / 256, 256, 0, st>>>(Q.G, nj, Q.lda, Q.perm, Q.eval);
     MUSED_CUDA(cudaGetLastError());
-    const int tm = (ell + GT - 1) / GT, tn = (int)((d + GT - 1) / GT);
-    k_merge_out<<<std::min(tm * tn, 8 * sm_count), 256, 0, st>>>(Q.M, ng, d, Q.Vq, Q.lda, Q.perm, Q.eval, ell,
-                                                                  o_sketch, o_vt, o_s2);
+    k_merge_out<false><<<std::min(tm * tn, 8 * sm_count), 256, 0, st>>>(Q.M, ng, d, Q.Vq, Q.lda, Q.perm, Q.eval, ell,
+                                                                       o_sketch, o_vt, o_s2);
     MUSED_CUDA(cudaGetLastError());
     COUNT_LAUNCH(3);
     return 0;
@@ -303,6 +434,25 @@ int merge_query_solve(const QueryScratch& Q, int ng, long long d, int ell, int s
 
 int merge_query(const QueryScratch& Q, int ng, long long d, int ell, int sm_count, double* o_sketch,
                 double* o_vt, double* o_s2, cudaStream_t st) {
+    // more rows than columns: eigensolve the d x d covariance instead of the ng x ng Gram
+    // (smaller, no structural null space, and its eigenvectors are the rows of Vt)
+    if (Q.VT && d < ng && d <= Q.lda && !getenv("MUSED_EIG_LEGACY") && !getenv("MUSED_EIG_NOCOV")) {
+        const int tiles = (int)((d + GT - 1) / GT);
+        k_cov_f64<<<std::min(tiles * tiles, 8 * sm_count), 256, 0, st>>>(Q.M, ng, d, Q.G, Q.lda);
+        MUSED_CUDA(cudaGetLastError());
+        bool done = false;
+        int npad = 0;
+        int rc = dispatch_eig_big(Q, (int)d, sm_count, st, &npad, &done);
+        if (rc) return rc;
+        if (done) {
+            k_sort_eigs<<<(npad + 255) / 256, 256, 0, st>>>(Q.lam, npad, 0, Q.perm, Q.eval);
+            k_cov_out<<<std::min(ell, 4 * sm_count), 256, 0, st>>>(Q.VT, Q.ldt, Q.perm, Q.eval, (int)d, ell, d, o_sketch,
+                                                                    o_vt, o_s2);
+            MUSED_CUDA(cudaGetLastError());
+            COUNT_LAUNCH(4);
+            return 0;
+        }
+    }
     int rc = merge_query_gram(Q, ng, d, sm_count, st);
     if (rc) return rc;
     return merge_query_solve(Q, ng, d, ell, sm_count, o_sketch, o_vt, o_s2, st);
@@ -452,8 +602,14 @@ static int engine_create(Engine** out, long long N, long long d, long long ell, 
         A_(Q.G, (size_t)Q.lda * Q.lda);
         A_(Q.Vq, (size_t)Q.lda * Q.lda);
         A_(Q.cs, (size_t)Q.ng_max);
-        A_(Q.eval, (size_t)Q.ng_max);
-        A_(Q.perm, (size_t)Q.ng_max);
+        Q.plan_big();
+        A_(Q.eval, (size_t)Q.npad_max);
+        A_(Q.perm, (size_t)Q.npad_max);
+        A_(Q.lam, (size_t)Q.npad_max);
+        A_(Q.VT, (size_t)Q.npad_max * Q.ldt);
+        A_(Q.mailL, Q.mail_count);
+        A_(Q.mailR, Q.mail_count);
+        A_(Q.sync, (size_t)QSYNC_WORDS);
         A_(Q.counters, 64);
         A_(Q.scr, 8);
     }
@@ -943,6 +1099,76 @@ int mused_fd_get(mused_fd_t* h, double* sketch, double* sigma2, double* vt, doub
     MUSED_REQUIRE(h && sketch && sigma2, "NULL argument");
     MUSED_CUDA(cudaSetDevice(h->E->device));
     return engine_get(*h->E, 0, false, sketch, sigma2, vt, delta, where, (cudaStream_t)stream);
+}
+
+int mused_sym_eig(const double* G, int64_t n, int64_t ld, double* evals, double* vecs, int64_t ld_vecs,
+                  int32_t* sweeps, void* stream) {
+    MUSED_REQUIRE(G && evals && vecs, "NULL argument");
+    MUSED_REQUIRE(n >= 1 && ld >= n && ld_vecs >= n, "bad shape n=%lld ld=%lld", (long long)n, (long long)ld);
+    cudaStream_t st = (cudaStream_t)stream;
+    int dev = 0;
+    MUSED_CUDA(cudaGetDevice(&dev));
+    cudaDeviceProp prop;
+    MUSED_CUDA(cudaGetDeviceProperties(&prop, dev));
+    QueryScratch Q;
+    Q.ng_max = (int)n + ((int)n & 1);
+    Q.lda = (int)ld;
+    Q.plan_big();
+    std::vector<void*> allocs;
+    auto alloc = [&](void** p, size_t bytes) -> int {
+        MUSED_CUDA(cudaMalloc(p, bytes));
+        allocs.push_back(*p);
+        return 0;
+    };
+    int rc = 0;
+    auto fail = [&](int code) { for (void* p : allocs) cudaFree(p); return code; };
+    if ((rc = alloc((void**)&Q.eval, sizeof(double) * Q.npad_max))) return fail(rc);
+    if ((rc = alloc((void**)&Q.perm, sizeof(int) * Q.npad_max))) return fail(rc);
+    if ((rc = alloc((void**)&Q.lam, sizeof(double) * Q.npad_max))) return fail(rc);
+    if ((rc = alloc((void**)&Q.VT, sizeof(double) * (size_t)Q.npad_max * Q.ldt))) return fail(rc);
+    if ((rc = alloc((void**)&Q.mailL, sizeof(double) * Q.mail_count))) return fail(rc);
+    if ((rc = alloc((void**)&Q.mailR, sizeof(double) * Q.mail_count))) return fail(rc);
+    if ((rc = alloc((void**)&Q.sync, sizeof(unsigned long long) * QSYNC_WORDS))) return fail(rc);
+    Q.G = const_cast<double*>(G);
+    bool done = false;
+    int npad = 0;
+    const int sm = prop.multiProcessorCount;
+    rc = dispatch_eig_big(Q, (int)n, sm, st, &npad, &done);
+    if (rc) return fail(rc);
+    if (!done) {
+        set_error("mused_sym_eig: n=%lld does not fit the shared memory of %d SMs", (long long)n, sm);
+        return fail(MUSED_ERR_ARG);
+    }
+    k_sort_eigs<<<(npad + 255) / 256, 256, 0, st>>>(Q.lam, npad, 0, Q.perm, Q.eval);
+    k_eig_permute_out<<<std::min((int)n, 4 * sm), 256, 0, st>>>(Q.VT, Q.ldt, Q.perm, Q.eval, (int)n, evals, vecs,
+                                                               (long long)ld_vecs);
+    COUNT_LAUNCH(3);
+    int info[2] = {0, 0};
+    cudaError_t e = cudaMemcpyAsync(info, Q.sync + 640, sizeof(info), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) {
+        set_error("mused_sym_eig failed: %s", cudaGetErrorString(e));
+        return fail(MUSED_ERR_CUDA);
+    }
+    if (sweeps) *sweeps = info[0];
+    if (getenv("MUSED_EIG_DEBUG")) {
+        unsigned long long h[QSYNC_WORDS];
+        cudaMemcpy(h, Q.sync, sizeof(h), cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[eig_big] n=%lld npad=%d sweeps=%d  cosines:", (long long)n, npad, info[0]);
+        for (int k = 0; k < info[0] && k < 64; ++k) {
+            double v;
+            memcpy(&v, &h[512 + k], 8);
+            fprintf(stderr, " %.1e", v);
+        }
+        fprintf(stderr, "\n[eig_big] Mcycles gram %.2f small %.2f apply %.2f out %.2f wait %.2f in %.2f\n", h[700] * 1e-6,
+                h[701] * 1e-6, h[702] * 1e-6, h[703] * 1e-6, h[704] * 1e-6, h[705] * 1e-6);
+    }
+    for (void* p : allocs) cudaFree(p);
+    if (info[1]) {
+        set_error("mused_sym_eig: a neighbour exchange timed out");
+        return MUSED_ERR_STATE;
+    }
+    return 0;
 }
 
 }  // extern "C"

@@ -1,6 +1,9 @@
 """GPU: the column-sharded driver on the CUDA shard engine.  Single process
 (world size 1) checks that the phase C ABI (stage / chunk_gram / chunk_finish /
-get_begin / get_finish) reproduces the plain fit()/get() path bit for bit; the
+get_begin / get_finish) reproduces the plain fit()/get() path: identical
+schedule and snapshot stamps, and the same query result up to row signs and
+round-off (the single-GPU get() eigensolves the smaller of the stack's Gram
+and covariance, the sharded one always the allreduced Gram); the
 2-rank NCCL run is tools/sharded_check.py under torchrun (needs 2 GPUs)."""
 import numpy as np
 import pytest
@@ -25,9 +28,15 @@ def test_phase_api_equals_fit_get_single_rank():
         pos += step
         if pos >= N:
             ga, gb = a.get(), b.get()
-            np.testing.assert_array_equal(ga[0], gb[0])
-            np.testing.assert_array_equal(ga[1], gb[1])
-            np.testing.assert_array_equal(ga[2], gb[2])
+            smax = float(np.max(ga[1]))
+            np.testing.assert_allclose(ga[1], gb[1], rtol=0, atol=1e-10 * smax)
+            for k in (0, 2):
+                sign = np.sign(np.einsum("ij,ij->i", ga[k], gb[k]))
+                sign[sign == 0] = 1.0
+                scale = np.sqrt(smax) if k == 0 else 1.0
+                keep = ga[1] > 1e-6 * smax          # directions of (numerically) zero rows are arbitrary
+                np.testing.assert_allclose((ga[k] * sign[:, None])[keep], gb[k][keep], rtol=0, atol=1e-6 * scale)
+            np.testing.assert_allclose(ga[0].T @ ga[0], gb[0].T @ gb[0], rtol=0, atol=1e-9 * smax)
             assert ga[3] == gb[3] and a.last_level == b.last_level and a.get_size() == b.get_size()
     for x, y in zip(a.debug_state(), b.debug_state()):
         assert x["q_t"] == y["q_t"] and x["q_s"] == y["q_s"]
