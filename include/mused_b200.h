@@ -181,6 +181,8 @@ int mused_fd_get(mused_fd_t* h, double* sketch, double* sigma2, double* vt, doub
  * ------------------------------------------------------------------------- */
 #define MUSED_METRIC_COSINE 0 /* matrix_operations.py:106 cosine_similarity          */
 #define MUSED_METRIC_L2 1     /* :118 NearestNeighbors (Euclidean), :286-289 argmin  */
+#define MUSED_METRIC_HAVERSINE 2 /* :22-30 location kNN, haversine_distance :250-263 (float64 entry) */
+#define MUSED_METRIC_L1SUM 3  /* :32-53 time: |d datetaken| + |d dateupload| (float64 entry)       */
 
 /* Fused cosine-similarity + threshold + argmax event assignment (north_star
  * operator; nearest reference code matrix_operations.py:106 and :286-289).
@@ -201,6 +203,15 @@ int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float
  * exactly like the reference: the top-k list may contain i itself). */
 int mused_topk_adjacency(const float* feats, int64_t W, int64_t f, int64_t ld, int metric,
                          int64_t k, uint8_t* adj, void* stream);
+
+/* Same operator for the two low-dimensional float64 modalities of
+ * create_adjacency_matrix: metric HAVERSINE ("location", matrix_operations.py:22-30,
+ * rows = (latitude, longitude) in degrees, k = k_basis + 1 there) and L1SUM
+ * ("time", :32-53, rows = (datetaken, dateupload), k = 3 k_basis + 1 there).
+ * Epoch seconds and degrees need float64: feats is W x f float64 device.
+ * The caller drops invalid rows first (NaN / zero stamps, :24 and :35). */
+int mused_topk_adjacency_f64(const double* feats, int64_t W, int64_t f, int64_t ld, int metric,
+                             int64_t k, uint8_t* adj, void* stream);
 
 /* Contingency table for match_clusters (matrix_operations.py:169-172):
  * counts[p * Q + q] = #{i : prev[i] == p and cur[i] == q}; labels outside

@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(HERE, "libmused_b200.so")
 
 F64, F32, I64, I32, U8 = 0, 1, 2, 3, 4
 HOST, DEVICE = 0, 1
-METRIC_COSINE, METRIC_L2 = 0, 1
+METRIC_COSINE, METRIC_L2, METRIC_HAVERSINE, METRIC_L1SUM = 0, 1, 2, 3
 
 _NP_DTYPES = {np.dtype(np.float64): F64, np.dtype(np.float32): F32, np.dtype(np.int64): I64,
               np.dtype(np.int32): I32, np.dtype(np.uint8): U8, np.dtype(np.bool_): U8}
@@ -45,6 +45,7 @@ SYMBOLS = [
     "mused_fd_create", "mused_fd_destroy", "mused_fd_fit", "mused_fd_fit_batches",
     "mused_fd_dump", "mused_fd_flush", "mused_fd_get",
     "mused_assign", "mused_topk_adjacency", "mused_contingency", "mused_sym_eig",
+    "mused_topk_adjacency_f64",
 ]
 
 
@@ -91,6 +92,7 @@ def load():
     lib.mused_assign.argtypes = [vp, i64, i64, i64, vp, i64, i64, C.c_int, C.c_float, vp, vp, vp]
     lib.mused_topk_adjacency.argtypes = [vp, i64, i64, i64, C.c_int, i64, vp, vp]
     lib.mused_contingency.argtypes = [vp, vp, i64, i32, i32, vp, vp]
+    lib.mused_topk_adjacency_f64.argtypes = [vp, i64, i64, i64, C.c_int, i64, vp, vp]
     lib.mused_sym_eig.argtypes = [vp, i64, i64, vp, vp, i64, C.POINTER(i32), vp]
     _lib = lib
     return lib

@@ -411,6 +411,16 @@ static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t 
     A.ringS = E.D.ringS;
     A.ringT = E.D.ringT;
     A.tol = 1e-3;          // quadratic phase: the sweep that measures <= 1e-3 leaves ~1e-6 (Gram accuracy)
+    {
+        static int sort_flag = -1;
+        static double tol_env = 0.0;
+        if (sort_flag < 0) {
+            sort_flag = getenv("MUSED_EIG_SORT") ? atoi(getenv("MUSED_EIG_SORT")) : 0;
+            tol_env = getenv("MUSED_EIG_TOL") ? atof(getenv("MUSED_EIG_TOL")) : 0.0;
+            MUSED_CUDA(cudaMemcpyToSymbol(g_eig_sort, &sort_flag, sizeof(int)));
+        }
+        if (tol_env > 0.0) A.tol = tol_env;
+    }
     A.max_sweeps = 24;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(E.D.S * EPL));

@@ -96,6 +96,7 @@ __device__ __forceinline__ double rcp_approx(double x) {         // MUFU.RCP64H:
     return y;
 }
 __device__ __forceinline__ double sel(bool p, double a, double b) { return p ? a : b; }
+__constant__ int g_eig_sort;   // experiment: keep the larger column first (de Rijk)
 
 // Hestenes rotation of a column pair with inner product g and squared norms
 // (nx, ny): branch-free, float64 pipe only (no fp32 detour: F2F conversions and
@@ -125,6 +126,10 @@ __device__ __forceinline__ void jacobi_angle(double g, double nx, double ny, dou
     const double cc = c * c, ss = s * s, cs2 = (c + c) * s * g;
     mx = fma(cc, nx, fma(ss, ny, -cs2));     // |c x - s y|^2
     my = fma(ss, nx, fma(cc, ny, cs2));      // |s x + c y|^2
+    if (g_eig_sort && mx < my) {             // x'' = s x + c y, y'' = -c x + s y
+        const double c1 = s, s1 = -c, m1 = my;
+        c = c1; s = s1; my = mx; mx = m1;
+    }
 }
 
 // Four independent rotations (column ids A_k, B_k of the warp's eight columns).

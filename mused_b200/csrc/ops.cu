@@ -4,7 +4,9 @@
 //   mused_topk_adjacency  kNN -> 0/1 adjacency, OR-fused (matrix_operations.py:101-141)
 //   mused_contingency     overlap counts of match_clusters (matrix_operations.py:169-172)
 #include <float.h>
+#include <stdlib.h>
 #include "common.cuh"
+#include "assign_tc.cuh"
 
 namespace mused {
 
@@ -169,25 +171,28 @@ __global__ void __launch_bounds__(256) k_pair_keys(const float* __restrict__ F, 
 }
 
 // per row: k best keys (ties -> lowest index), adj[i][j] |= 1 for j != i.
-__global__ void __launch_bounds__(256) k_topk_rows(const float* __restrict__ S, long long W, long long k,
+template <typename T>
+__global__ void __launch_bounds__(256) k_topk_rows(const T* __restrict__ S, long long W, long long k,
                                                    unsigned char* __restrict__ adj) {
-    extern __shared__ float row[];
-    __shared__ float rb[8];
+    extern __shared__ __align__(8) unsigned char row_raw[];
+    T* row = reinterpret_cast<T*>(row_raw);
+    __shared__ T rb[8];
     __shared__ int ri[8];
     for (long long i = blockIdx.x; i < W; i += gridDim.x) {
         for (long long c = threadIdx.x; c < W; c += 256) row[c] = S[(size_t)i * W + c];
         __syncthreads();
         const long long kk = k < W ? k : W;
+        const T lowest = (T)(-FLT_MAX);            // keys are >= -FLT_MAX in both precisions
         for (long long it = 0; it < kk; ++it) {
-            float b = -FLT_MAX;
+            T b = lowest;
             int bi = 0x7fffffff;
             for (long long c = threadIdx.x; c < W; c += 256) {
-                const float v = row[c];
+                const T v = row[c];
                 if (v > b) { b = v; bi = (int)c; }
             }
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
-                const float ob = __shfl_xor_sync(0xffffffffu, b, o);
+                const T ob = __shfl_xor_sync(0xffffffffu, b, o);
                 const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
                 if (ob > b || (ob == b && oi < bi)) { b = ob; bi = oi; }
             }
@@ -197,12 +202,39 @@ __global__ void __launch_bounds__(256) k_topk_rows(const float* __restrict__ S, 
                 for (int q = 1; q < 8; ++q)
                     if (rb[q] > b || (rb[q] == b && ri[q] < bi)) { b = rb[q]; bi = ri[q]; }
                 if (bi != 0x7fffffff) {
-                    row[bi] = -FLT_MAX;  // taken (an all -FLT_MAX row simply stops matching)
+                    row[bi] = lowest;  // taken (an all -FLT_MAX row simply stops matching)
                     if (bi != (int)i) adj[(size_t)i * W + bi] = 1;
                 }
             }
             __syncthreads();
         }
+    }
+}
+
+// float64 keys of the two low-dimensional modalities (larger = closer):
+//   HAVERSINE  (matrix_operations.py:22-30, :250-263): rows are (latitude, longitude) in degrees;
+//              key = -a with a = sin^2(dlat/2) + cos(lat1) cos(lat2) sin^2(dlon/2); the distance
+//              2 r asin(sqrt(a)) is monotone in a, so the ranking is the reference's.
+//   L1SUM      (:32-53): key = -(|x0 - y0| + |x1 - y1| + ...), the reference's taken + upload differences.
+__global__ void __launch_bounds__(256) k_pair_keys_f64(const double* __restrict__ F, long long W, long long f,
+                                                       long long ld, int metric, double* __restrict__ S) {
+    const double rad = 0.017453292519943295;
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < W * W;
+         e += (long long)gridDim.x * blockDim.x) {
+        const long long r = e / W, c = e % W;
+        const double* x = F + r * ld;
+        const double* y = F + c * ld;
+        double key;
+        if (metric == MUSED_METRIC_HAVERSINE) {
+            const double lat1 = x[0] * rad, lon1 = x[1] * rad, lat2 = y[0] * rad, lon2 = y[1] * rad;
+            const double sa = sin((lat2 - lat1) / 2.0), sb = sin((lon2 - lon1) / 2.0);
+            key = -(sa * sa + cos(lat1) * cos(lat2) * sb * sb);
+        } else {
+            double acc = 0.0;
+            for (long long j = 0; j < f; ++j) acc += fabs(y[j] - x[j]);
+            key = -acc;
+        }
+        S[e] = fmax(key, -(double)FLT_MAX);
     }
 }
 
@@ -226,6 +258,25 @@ static int sm_count_of_current() {
 using namespace mused;
 extern "C" void mused_count_launches(uint64_t n);
 
+// tensor-core path of mused_assign (assign_tc.cuh); *done = false -> shape not eligible
+template <int MH>
+static int launch_assign_tc(const float* X, int64_t n, int64_t d, int64_t ld_x, int NP, const float* Chi,
+                            const float* Clo, atc::Args& A, cudaStream_t st) {
+    CUtensorMap tx, thi, tlo;
+    if (encode_tmap_f32_2d(&tx, X, (uint64_t)n, (uint64_t)d, (uint64_t)ld_x, 128) != CUDA_SUCCESS ||
+        encode_tmap_f32_2d(&thi, Chi, (uint64_t)NP, (uint64_t)d, (uint64_t)d, (uint32_t)NP) != CUDA_SUCCESS ||
+        encode_tmap_f32_2d(&tlo, Clo, (uint64_t)NP, (uint64_t)d, (uint64_t)d, (uint32_t)NP) != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed for the assignment operands");
+        return MUSED_ERR_CUDA;
+    }
+    const size_t smem = atc::Cfg<MH>::smem_bytes(NP);
+    MUSED_CUDA(cudaFuncSetAttribute(atc::k_assign_tc<MH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long long tiles = (n + MH * 128 - 1) / (MH * 128);
+    atc::k_assign_tc<MH><<<(unsigned)tiles, atc::Cfg<MH>::NTHREADS, smem, st>>>(tx, thi, tlo, A);
+    MUSED_CUDA(cudaGetLastError());
+    return 0;
+}
+
 extern "C" {
 
 int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float* C, int64_t k,
@@ -235,6 +286,30 @@ int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float
     MUSED_REQUIRE(metric == MUSED_METRIC_COSINE || metric == MUSED_METRIC_L2, "unknown metric %d", metric);
     if (n == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
+    // tensor-core path: K in whole 128-byte rows, every centroid in one UMMA N, TMA-addressable X
+    const int NP = (int)((k + 15) / 16 * 16);
+    if (d % 32 == 0 && k <= 256 && ld_x % 4 == 0 && ((uintptr_t)X & 15) == 0 && n < (1ll << 31) &&
+        !getenv("MUSED_ASSIGN_SIMT")) {
+        float *Chi = nullptr, *Clo = nullptr, *c2 = nullptr;
+        MUSED_CUDA(cudaMallocAsync((void**)&Chi, sizeof(float) * (size_t)NP * d, st));
+        MUSED_CUDA(cudaMallocAsync((void**)&Clo, sizeof(float) * (size_t)NP * d, st));
+        MUSED_CUDA(cudaMallocAsync((void**)&c2, sizeof(float) * (size_t)NP, st));
+        atc::k_assign_prep<<<NP, 256, 0, st>>>(C, k, d, ld_c, NP, Chi, Clo, c2);
+        MUSED_CUDA(cudaGetLastError());
+        atc::Args A;
+        A.n = n; A.k = (int)k; A.NP = NP; A.kblocks = (int)(d / 32); A.metric = metric; A.tau = tau;
+        A.cn2 = c2; A.labels = labels; A.score = score;
+        const int sms = sm_count_of_current();
+        const bool two = atc::Cfg<2>::smem_bytes(NP) <= 227u * 1024u && (n + 255) / 256 >= sms;
+        int rc = two ? launch_assign_tc<2>(X, n, d, ld_x, NP, Chi, Clo, A, st)
+                     : launch_assign_tc<1>(X, n, d, ld_x, NP, Chi, Clo, A, st);
+        MUSED_CUDA(cudaFreeAsync(Chi, st));
+        MUSED_CUDA(cudaFreeAsync(Clo, st));
+        MUSED_CUDA(cudaFreeAsync(c2, st));
+        if (rc) return rc;
+        mused_count_launches(2);
+        return 0;
+    }
     float* cn2 = nullptr;
     MUSED_CUDA(cudaMallocAsync((void**)&cn2, sizeof(float) * (size_t)k, st));
     k_row_norm2_f32<<<(unsigned)((k + 7) / 8), 256, 0, st>>>(C, k, d, ld_c, cn2);
@@ -266,12 +341,35 @@ int mused_topk_adjacency(const float* feats, int64_t W, int64_t f, int64_t ld, i
     k_pair_keys<<<(int)std::min<long long>(tiles, 16ll * sms), 256, 0, st>>>(feats, W, f, ld, n2, metric, S);
     MUSED_CUDA(cudaGetLastError());
     const size_t smem = (size_t)W * sizeof(float);
-    MUSED_CUDA(cudaFuncSetAttribute(k_topk_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_topk_rows<<<(int)std::min<long long>(W, 8ll * sms), 256, smem, st>>>(S, W, k, adj);
+    MUSED_CUDA(cudaFuncSetAttribute(k_topk_rows<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_topk_rows<float><<<(int)std::min<long long>(W, 8ll * sms), 256, smem, st>>>(S, W, k, adj);
     MUSED_CUDA(cudaGetLastError());
     MUSED_CUDA(cudaFreeAsync(S, st));
     MUSED_CUDA(cudaFreeAsync(n2, st));
     mused_count_launches(3);
+    return 0;
+}
+
+int mused_topk_adjacency_f64(const double* feats, int64_t W, int64_t f, int64_t ld, int metric, int64_t k,
+                             uint8_t* adj, void* stream) {
+    MUSED_REQUIRE(W >= 1 && f >= 1 && ld >= f && k >= 0, "bad shape");
+    MUSED_REQUIRE(feats && adj, "NULL argument");
+    MUSED_REQUIRE(metric == MUSED_METRIC_HAVERSINE || metric == MUSED_METRIC_L1SUM, "unknown float64 metric %d", metric);
+    MUSED_REQUIRE(metric != MUSED_METRIC_HAVERSINE || f == 2, "haversine rows are (latitude, longitude)");
+    MUSED_REQUIRE(W * 8 <= 200 * 1024, "window of %lld rows exceeds the per-row shared-memory select (max 25600)", (long long)W);
+    if (k == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    double* S = nullptr;
+    MUSED_CUDA(cudaMallocAsync((void**)&S, sizeof(double) * (size_t)W * W, st));
+    const int sms = sm_count_of_current();
+    k_pair_keys_f64<<<(int)std::min<long long>((W * W + 255) / 256, 16ll * sms), 256, 0, st>>>(feats, W, f, ld, metric, S);
+    MUSED_CUDA(cudaGetLastError());
+    const size_t smem = (size_t)W * sizeof(double);
+    MUSED_CUDA(cudaFuncSetAttribute(k_topk_rows<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_topk_rows<double><<<(int)std::min<long long>(W, 8ll * sms), 256, smem, st>>>(S, W, k, adj);
+    MUSED_CUDA(cudaGetLastError());
+    MUSED_CUDA(cudaFreeAsync(S, st));
+    mused_count_launches(2);
     return 0;
 }
 

@@ -15,6 +15,8 @@ from . import _lib
 
 _METRIC = {"cosine": _lib.METRIC_COSINE, "text": _lib.METRIC_COSINE,
            "euclidean": _lib.METRIC_L2, "l2": _lib.METRIC_L2}
+_METRIC_F64 = {"haversine": _lib.METRIC_HAVERSINE, "location": _lib.METRIC_HAVERSINE,
+               "l1sum": _lib.METRIC_L1SUM, "time": _lib.METRIC_L1SUM}
 
 
 def _dev_f32(x, device):
@@ -51,9 +53,25 @@ def topk_adjacency(features, k, *, metric="cosine", out=None, device="cuda:0"):
     """kNN adjacency of one dense modality, OR-accumulated into ``out`` (uint8 W x W).
 
     cosine: matrix_operations.py:101-108 (k = k_basis + 1 there); euclidean:
-    :112-119 (k = k_basis); writer :123-130 (directed, no self edges).
+    :112-119 (k = k_basis); haversine ("location", :22-30, rows = latitude,
+    longitude in degrees) and l1sum ("time", :32-53, rows = datetaken,
+    dateupload) are computed in float64; writer :123-130 (directed, no self edges).
     """
     lib = _lib.load()
+    if metric in _METRIC_F64:
+        # degrees and epoch seconds need float64 (matrix_operations.py:22-53)
+        if isinstance(features, torch.Tensor):
+            F = features.to(device=device, dtype=torch.float64).contiguous()
+        else:
+            F = torch.as_tensor(np.ascontiguousarray(features, dtype=np.float64)).to(device)
+        W, f = F.shape
+        if out is None:
+            out = torch.zeros((W, W), dtype=torch.uint8, device=F.device)
+        with torch.cuda.device(F.device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(lib.mused_topk_adjacency_f64(F.data_ptr(), W, f, F.stride(0) if W > 1 else f,
+                                                    _METRIC_F64[metric], int(k), out.data_ptr(), st))
+        return out
     F = _dev_f32(features, device)
     W, f = F.shape
     if out is None:
@@ -68,19 +86,28 @@ def topk_adjacency(features, k, *, metric="cosine", out=None, device="cuda:0"):
 def create_adjacency_matrix(data, modality_type, k_basis=50, *, device="cuda:0"):
     """Dense numeric branches of matrix_operations.py:14-132 -> W x W float64 0/1 ndarray.
 
-    modality_type "text"/"cosine": rows are (TF-IDF or embedding) vectors, cosine top-(k_basis+1);
+    modality_type "location": (latitude, longitude) rows, haversine kNN, k = k_basis + 1;
+    "time": (datetaken, dateupload) rows, |d taken| + |d upload|, k = 3 k_basis + 1;
+    "text"/"cosine": rows are (TF-IDF or embedding) vectors, cosine top-(k_basis+1);
     anything else: Euclidean kNN with k = k_basis (the reference's default branch).
     """
     A = np.asarray(data, dtype=np.float64)
     W = A.shape[0]
     out = np.zeros((W, W))
-    valid = np.where(np.all(np.isfinite(A), axis=1))[0]           # :114
-    if len(valid) == 0:
-        return out
-    if modality_type in ("text", "cosine"):
+    if modality_type == "location":
+        valid = np.where(~np.isnan(A).any(axis=1))[0]              # :24
+        k, metric = k_basis + 1, "haversine"                       # :23
+    elif modality_type == "time":
+        valid = np.where(~((A[:, 0] == 0.0) | (A[:, 1] == 0.0)))[0]   # :35
+        k, metric = 3 * k_basis + 1, "l1sum"                       # :34
+    elif modality_type in ("text", "cosine"):
+        valid = np.where(np.all(np.isfinite(A), axis=1))[0]
         k, metric = k_basis + 1, "cosine"                          # :101
     else:
+        valid = np.where(np.all(np.isfinite(A), axis=1))[0]       # :114
         k, metric = max(1, k_basis), "euclidean"                   # :112, :118
+    if len(valid) == 0:
+        return out
     adj = topk_adjacency(A[valid], min(k, len(valid)), metric=metric, device=device).cpu().numpy()
     out[np.ix_(valid, valid)] = adj
     return out

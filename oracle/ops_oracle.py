@@ -6,7 +6,7 @@ function, so its parity is UNPINNED by any reference
 test -- the restatement follows sklearn's cosine_similarity semantics used at
 matrix_operations.py:106 (rows L2-normalised, zero rows keep norm 1) plus
 np.argmax, and the nearest-centroid rule of matrix_operations.py:286-289.
-``knn_adjacency`` follows matrix_operations.py:101-108 / :112-119 / :123-130 and
+``knn_adjacency`` follows matrix_operations.py:22-53 / :101-108 / :112-119 / :123-130 and
 is checked against the imported reference by tests/test_oracle_golden.py.
 """
 from __future__ import annotations
@@ -44,11 +44,29 @@ def l2_assign(X, C, tau):
     return labels, best, gap
 
 
+def haversine_km(F):
+    """Pairwise haversine distance of (latitude, longitude) rows in degrees,
+    matrix_operations.py:250-263 (r = 6371 km)."""
+    lat = np.radians(F[:, 0])
+    lon = np.radians(F[:, 1])
+    dlat = lat[None, :] - lat[:, None]
+    dlon = lon[None, :] - lon[:, None]
+    a = np.sin(dlat / 2) ** 2 + np.cos(lat)[:, None] * np.cos(lat)[None, :] * np.sin(dlon / 2) ** 2
+    return 2 * np.arcsin(np.sqrt(np.clip(a, 0.0, 1.0))) * 6371
+
+
 def knn_keys(F, metric):
     F = np.asarray(F, dtype=np.float64)
     if metric == "cosine":
         Fn = _normalize(F)
         return Fn @ Fn.T
+    if metric == "haversine":                                  # matrix_operations.py:22-30
+        return -haversine_km(F)
+    if metric == "l1sum":                                      # matrix_operations.py:40-50
+        K = np.zeros((len(F), len(F)))
+        for j in range(F.shape[1]):
+            K -= np.abs(F[None, :, j] - F[:, None, j])
+        return K
     sq = (F * F).sum(1)
     K = -np.maximum(sq[:, None] + sq[None, :] - 2 * F @ F.T, 0)
     np.fill_diagonal(K, 0.0)

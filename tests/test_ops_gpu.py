@@ -29,6 +29,29 @@ def test_cosine_assign(n, d, k):
     assert sure.mean() > 0.99
 
 
+def test_cosine_assign_tensor_core_tiles_and_simt_agree(monkeypatch):
+    """n >= 148 * 256 takes the two-accumulator tile of assign_tc.cuh, a ragged tail included; the
+    fp32 SIMT kernel (shapes the tensor-core path does not take) must give the same labels."""
+    from mused_b200 import matrix_operations as mo
+    rng = np.random.default_rng(11)
+    n, d, k = 148 * 256 + 77, 256, 150
+    C = rng.standard_normal((k, d)).astype(np.float32)
+    X = (C[rng.integers(0, k, n)] + 0.8 * rng.standard_normal((n, d))).astype(np.float32)
+    X[5] = 0.0
+    ref, best, gap = ops_oracle.cosine_assign(X, C, 0.3)
+    sure = (gap > TIE) & (np.abs(best - 0.3) > TIE)
+    lab, score = mo.cosine_assign(X, C, 0.3, return_score=True)
+    assert np.array_equal(lab.cpu().numpy()[sure], ref[sure]) and sure.mean() > 0.99
+    np.testing.assert_allclose(score.cpu().numpy(), best, rtol=1e-4, atol=1e-4)
+    l2ref, l2best, l2gap = ops_oracle.l2_assign(X, C, -1.0)
+    l2 = mo.cosine_assign(X, C, -1.0, metric="l2").cpu().numpy()
+    s2 = l2gap > 1e-3
+    assert np.array_equal(l2[s2], l2ref[s2])
+    monkeypatch.setenv("MUSED_ASSIGN_SIMT", "1")
+    lab2 = mo.cosine_assign(X[:5000], C, 0.3).cpu().numpy()
+    assert np.array_equal(lab2[sure[:5000]], ref[:5000][sure[:5000]])
+
+
 def test_cosine_assign_edge_cases():
     from mused_b200 import matrix_operations as mo
     d = 40
@@ -74,6 +97,43 @@ def test_topk_adjacency(W, f, k, metric):
     out = torch.as_tensor(adj.copy()).cuda()
     mo.topk_adjacency(F, k, metric=metric, out=out)
     assert np.array_equal(out.cpu().numpy(), adj)
+
+
+@pytest.mark.parametrize("W,k", [(400, 51), (2000, 151), (3, 7)])
+def test_topk_adjacency_location_and_time(W, k):
+    """float64 modalities of create_adjacency_matrix (matrix_operations.py:22-53)."""
+    from mused_b200 import matrix_operations as mo
+    rng = np.random.default_rng(W)
+    loc = np.column_stack([rng.uniform(-70, 70, W), rng.uniform(-180, 180, W)])
+    ref, margin = ops_oracle.knn_adjacency(loc, k, "haversine")
+    adj = mo.topk_adjacency(loc, k, metric="haversine").cpu().numpy()
+    sure = margin > 1e-9
+    assert np.array_equal(adj[sure], ref[sure]) and (sure.mean() > 0.99 or W < 10)
+    tm = np.column_stack([1.3e9 + rng.uniform(0, 3e6, W), 1.3e9 + rng.uniform(0, 3e6, W)])
+    ref, margin = ops_oracle.knn_adjacency(tm, k, "l1sum")
+    adj = mo.topk_adjacency(tm, k, metric="l1sum").cpu().numpy()
+    sure = margin > 0                                    # same float64 operations: exact unless tied
+    assert np.array_equal(adj[sure], ref[sure]) and (sure.mean() > 0.99 or W < 10)
+    assert np.all(adj.diagonal() == 0)
+
+
+def test_create_adjacency_location_time_validity_rules():
+    from mused_b200 import matrix_operations as mo
+    rng = np.random.default_rng(2)
+    loc = np.column_stack([rng.uniform(-60, 60, 90), rng.uniform(-180, 180, 90)])
+    loc[11, 1] = np.nan
+    A = mo.create_adjacency_matrix(loc, "location", k_basis=6)
+    valid = np.where(~np.isnan(loc).any(axis=1))[0]
+    ref, margin = ops_oracle.knn_adjacency(loc[valid], 7, "haversine")
+    assert np.array_equal(A[np.ix_(valid, valid)], ref.astype(float))
+    assert A[11].sum() == 0 and A[:, 11].sum() == 0
+    tm = np.column_stack([1.3e9 + rng.uniform(0, 1e6, 90), 1.3e9 + rng.uniform(0, 1e6, 90)])
+    tm[3, 1] = 0.0
+    A = mo.create_adjacency_matrix(tm, "time", k_basis=4)
+    valid = np.where(~((tm[:, 0] == 0.0) | (tm[:, 1] == 0.0)))[0]
+    ref, margin = ops_oracle.knn_adjacency(tm[valid], 13, "l1sum")
+    assert np.array_equal(A[np.ix_(valid, valid)], ref.astype(float))
+    assert A[3].sum() == 0 and A[:, 3].sum() == 0
 
 
 def test_create_adjacency_and_fuse_match_reference_semantics():

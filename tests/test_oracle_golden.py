@@ -103,6 +103,27 @@ def test_knn_adjacency_oracle_vs_reference_default_branch(capsys):
     assert np.array_equal(a2, ((ref + ref.T) > 0).astype(int))
 
 
+@pytest.mark.skipif(not ref_shim.available(), reason="reference tree not present (GPU box)")
+def test_knn_adjacency_oracle_vs_reference_location_and_time_branches(capsys):
+    swfd, mo, me = ref_shim.load()
+    rng = np.random.default_rng(5)
+    loc = np.column_stack([rng.uniform(-60, 60, 50), rng.uniform(-180, 180, 50)])
+    loc[4] = np.nan                                               # matrix_operations.py:24
+    ref = mo.create_adjacency_matrix(loc, "location", k_basis=4)  # :22-30, k = 5
+    valid = np.where(~np.isnan(loc).any(axis=1))[0]
+    adj, margin = ops_oracle.knn_adjacency(loc[valid], 5, "haversine")
+    assert margin.min() > 1e-9
+    assert np.array_equal(ref[np.ix_(valid, valid)].astype(np.uint8), adj)
+    assert ref[4].sum() == 0 and ref[:, 4].sum() == 0
+    tm = np.column_stack([1.3e9 + rng.uniform(0, 1e6, 40), 1.3e9 + rng.uniform(0, 1e6, 40)])
+    tm[9, 0] = 0.0                                                # :35
+    ref = mo.create_adjacency_matrix(tm, "time", k_basis=3)       # :32-53, k = 10
+    valid = np.where(~((tm[:, 0] == 0.0) | (tm[:, 1] == 0.0)))[0]
+    adj, margin = ops_oracle.knn_adjacency(tm[valid], 10, "l1sum")
+    assert margin.min() > 0
+    assert np.array_equal(ref[np.ix_(valid, valid)].astype(np.uint8), adj)
+
+
 def test_cosine_assign_oracle_properties():
     rng = np.random.default_rng(0)
     C = rng.standard_normal((9, 33))
