@@ -161,3 +161,36 @@ def match_clusters(prev_clusters, new_clusters, method="hungarian", min_overlap=
     row_ind, col_ind = linear_sum_assignment(cost)
     mapping = {unique_new[c]: unique_prev[r] for r, c in zip(row_ind, col_ind)}
     return np.array([mapping.get(c, c) for c in new_clusters])
+
+
+def nearest_centroid(X, centroids, *, device="cuda:0"):
+    """argmin_j ||x_i - c_j|| on the GPU (KMeans E-step / predict; matrix_operations.py:286-289)."""
+    return cosine_assign(X, centroids, -1.0, metric="l2", device=device)
+
+
+def perform_clustering(matrix, n_clusters, seed, *, device="cuda:0", return_model=False):
+    """KMeans labels of the reduced window (matrix_operations.py:149-153).
+
+    ``KMeans(n_clusters, random_state=seed).fit`` stays sklearn's (k-means++ seeding and Lloyd
+    updates are not reproducible bit for bit on another implementation, SURVEY.md 7.3-6, and label
+    identity with the reference is the parity gate); the assignment of every item to its nearest
+    centre -- what ``fit_predict`` returns -- is the device operator ``nearest_centroid``.  Items
+    whose two nearest centres are closer than fp32 resolution keep sklearn's label.
+    """
+    from sklearn.cluster import KMeans
+    M = np.ascontiguousarray(np.asarray(matrix, dtype=np.float64))
+    km = KMeans(n_clusters=n_clusters, random_state=seed).fit(M)
+    C = km.cluster_centers_
+    lab, dist = cosine_assign(M, C, -1.0, metric="l2", device=device, return_score=True)
+    lab = lab.cpu().numpy().astype(km.labels_.dtype)
+    diff = lab != km.labels_
+    if diff.any():
+        # near-ties at fp32 resolution: documented exception of parity gate (3)
+        idx = np.where(diff)[0]
+        d_dev = np.linalg.norm(M[idx] - C[lab[idx]], axis=1)
+        d_skl = np.linalg.norm(M[idx] - C[km.labels_[idx]], axis=1)
+        tie = np.abs(d_dev - d_skl) <= 1e-5 * np.maximum(d_skl, 1e-30) + 1e-6 * float(np.abs(M).max() + 1e-30)
+        if not tie.all():
+            raise RuntimeError("device nearest-centroid labels differ from KMeans beyond near-ties")
+        lab[idx] = km.labels_[idx]
+    return (lab, km) if return_model else lab

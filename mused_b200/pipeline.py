@@ -1,0 +1,56 @@
+"""The SWFDMC window loop of /root/reference/main.py:25-119 on the device operators.
+
+Same steps, same order, same arguments as ``process_streaming_data(approach="SWFDMC")``:
+per full window -- one kNN adjacency per modality (create_adjacency_matrix, :44-49), OR-fusion
+(:56), the rows of the fused W x W matrix through the sliding-window FD sketch (:60-67), ``get()``
+and the transpose fix-up (:70-76), KMeans (:97), Hungarian matching with the previous window
+(:106-110).  String modalities (username / tags / text) are host-side string processing in the
+reference and are not taken here.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import matrix_operations as mo
+from .swfd import SeqBasedSWFD
+
+
+def process_streaming_data(data_modalities, modality_types, complete_true_labels, *, window_size=2000,
+                           reduced_dim=50, k_basis=50, seed=0, step_window_ratio=1, schedule="reference",
+                           device="cuda:0"):
+    """Returns (all_clusters, all_true_labels, per-window list of reduced matrices)."""
+    subset_size = len(complete_true_labels)
+    window, all_clusters, all_true, reduced = [], [], [], []
+    swfd, prev_clusters = None, None
+    for i in range(subset_size):
+        window.append(i)
+        if len(window) > window_size:
+            window.pop(0)
+        if len(window) == window_size and (i + 1) * step_window_ratio % window_size == 0:   # main.py:32
+            lo = i - window_size + 1
+            true_labels = np.asarray(complete_true_labels[lo:i + 1])
+            all_true.extend(true_labels)
+            n_clusters = len(np.unique(true_labels))                                          # main.py:41
+            mats = [mo.create_adjacency_matrix(np.asarray(m[lo:i + 1]), t, k_basis=k_basis, device=device)
+                    for m, t in zip(data_modalities, modality_types)]                         # main.py:44-49
+            fused = mo.fuse_matrices(mats)                                                    # main.py:56
+            if swfd is None:                                                                  # main.py:60-62
+                max_norm = float(np.max(np.linalg.norm(fused, axis=1) ** 2))
+                swfd = SeqBasedSWFD(N=window_size, R=max_norm, d=fused.shape[1], sketch_dim=reduced_dim,
+                                    schedule=schedule, device=device)
+            swfd.fit(fused)                                   # main.py:65-67, the W rows in one call
+            red = swfd.get()[0]                               # main.py:70
+            red = np.asarray(red.cpu() if hasattr(red, "cpu") else red)
+            if red.shape[0] != window_size:                   # main.py:73-76
+                red = red.T
+            reduced.append(red)
+            clusters = mo.perform_clustering(red, n_clusters, seed, device=device)            # main.py:97
+            clusters = mo.match_clusters(prev_clusters, clusters, method="hungarian", min_overlap=3,
+                                         device=device)                                       # main.py:110
+            if clusters is None or len(clusters) == 0:
+                clusters = np.full(window_size, 0)
+            prev_clusters = clusters
+            all_clusters.extend(clusters)
+    if swfd is not None:
+        swfd.close()
+    return np.asarray(all_clusters), np.asarray(all_true), reduced
