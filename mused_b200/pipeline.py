@@ -37,7 +37,8 @@ def process_streaming_data(data_modalities, modality_types, complete_true_labels
             if swfd is None:                                                                  # main.py:60-62
                 max_norm = float(np.max(np.linalg.norm(fused, axis=1) ** 2))
                 swfd = SeqBasedSWFD(N=window_size, R=max_norm, d=fused.shape[1], sketch_dim=reduced_dim,
-                                    schedule=schedule, device=device)
+                                    schedule=schedule,
+                                    device=int(str(device).split(":")[-1]) if ":" in str(device) else 0)
             swfd.fit(fused)                                   # main.py:65-67, the W rows in one call
             red = swfd.get()[0]                               # main.py:70
             red = np.asarray(red.cpu() if hasattr(red, "cpu") else red)
