@@ -390,9 +390,12 @@ static int launch_gram(BEngine& E, cudaStream_t st) {
 template <int EPL>
 static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t st) {
     static bool attr_set = false;
+    static bool p2p = false;
     const int smem = (int)sizeof(EigSmem<EPL>);
     if (!attr_set) {
-        MUSED_CUDA(cudaFuncSetAttribute(k_eig_jacobi<EPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        p2p = getenv("MUSED_EIG_P2P") && atoi(getenv("MUSED_EIG_P2P")) != 0;
+        MUSED_CUDA(cudaFuncSetAttribute(k_eig_jacobi<EPL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        MUSED_CUDA(cudaFuncSetAttribute(k_eig_jacobi<EPL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_set = true;
     }
     EigArgs A;
@@ -411,17 +414,6 @@ static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t 
     A.ringS = E.D.ringS;
     A.ringT = E.D.ringT;
     A.tol = 1e-3;          // quadratic phase: the sweep that measures <= 1e-3 leaves ~1e-6 (Gram accuracy)
-    {
-        static int sort_flag = -1;
-        static double tol_env = 0.0;
-        if (sort_flag < 0) {
-            sort_flag = getenv("MUSED_EIG_SORT") ? atoi(getenv("MUSED_EIG_SORT")) : 0;
-            tol_env = getenv("MUSED_EIG_TOL") ? atof(getenv("MUSED_EIG_TOL")) : 0.0;
-            MUSED_CUDA(cudaMemcpyToSymbol(g_eig_sort, &sort_flag, sizeof(int)));
-        }
-        if (tol_env > 0.0) A.tol = tol_env;
-    }
-    A.max_sweeps = 24;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(E.D.S * EPL));
     cfg.blockDim = dim3(EIG_NT);
@@ -434,7 +426,8 @@ static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t 
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    MUSED_CUDA(cudaLaunchKernelEx(&cfg, k_eig_jacobi<EPL>, A));
+    if (p2p) MUSED_CUDA(cudaLaunchKernelEx(&cfg, k_eig_jacobi<EPL, true>, A));
+    else MUSED_CUDA(cudaLaunchKernelEx(&cfg, k_eig_jacobi<EPL, false>, A));
     return 0;
 }
 

@@ -65,6 +65,12 @@ struct EigSmem {
     double red_off[64];                   // per-warp partial maxima, collected in CTA 0
     double red_nmax[64];
     double cut;
+    // point-to-point exchange: slotA / slotB double as the INCOMING blocks (pushed by the
+    // neighbour), one mbarrier per slot counts the 32 lanes of the producer warp
+    double park[EIG_C][N2];               // position 0 sits the odd round out (warp 0 of the cluster)
+    double parkn[EIG_C];
+    unsigned long long fullA[EIG_WARPS];
+    unsigned long long fullB[EIG_WARPS];
 };
 
 // ---- distributed shared memory by cluster address -----------------------------------------
@@ -85,6 +91,30 @@ __device__ __forceinline__ void cluster_barrier() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ void mbar_init_cta(unsigned long long* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_remote_arrive(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// bounded: a protocol bug traps (the launch fails) instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait_cluster(unsigned long long* bar, uint32_t parity) {
+    const uint32_t a = (uint32_t)__cvta_generic_to_shared(bar);
+    for (uint32_t spin = 0;; ++spin) {
+        uint32_t ok;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(a), "r"(parity)
+            : "memory");
+        if (ok) return;
+        if (spin > (1u << 24)) __trap();
+    }
+}
+
 __device__ __forceinline__ double rsqrt_approx(double x) {       // MUFU.RSQ64H: ~20 bits
     double y;
     asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
@@ -96,7 +126,6 @@ __device__ __forceinline__ double rcp_approx(double x) {         // MUFU.RCP64H:
     return y;
 }
 __device__ __forceinline__ double sel(bool p, double a, double b) { return p ? a : b; }
-__constant__ int g_eig_sort;   // experiment: keep the larger column first (de Rijk)
 
 // Hestenes rotation of a column pair with inner product g and squared norms
 // (nx, ny): branch-free, float64 pipe only (no fp32 detour: F2F conversions and
@@ -126,10 +155,6 @@ __device__ __forceinline__ void jacobi_angle(double g, double nx, double ny, dou
     const double cc = c * c, ss = s * s, cs2 = (c + c) * s * g;
     mx = fma(cc, nx, fma(ss, ny, -cs2));     // |c x - s y|^2
     my = fma(ss, nx, fma(cc, ny, cs2));      // |s x + c y|^2
-    if (g_eig_sort && mx < my) {             // x'' = s x + c y, y'' = -c x + s y
-        const double c1 = s, s1 = -c, m1 = my;
-        c = c1; s = s1; my = mx; mx = m1;
-    }
 }
 
 // Four independent rotations (column ids A_k, B_k of the warp's eight columns).
@@ -259,8 +284,85 @@ __device__ __forceinline__ void jacobi_iteration(EigSmem<EPL>& sm, double (&col)
     }
 }
 
+// Point-to-point variant of the same two rounds (opt-in, MUSED_EIG_P2P=1; measured on B200 at
+// configs[1]: 1.74 ms per chunk against 1.65 ms with the two cluster barriers -- the iteration is
+// bound by the reduce -> angle -> broadcast latency chain of its eight rotation steps, not by the
+// exchange): a block that leaves is PUSHED into the
+// neighbour's shared memory (st.shared::cluster) and announced on the neighbour's mbarrier
+// (release.cluster, one arrival per lane); the receiver polls its own barrier and reads local
+// shared memory.  No cluster-wide barrier inside a sweep: warps only wait for the neighbour they
+// exchange with.  A slot is rewritten only after its reader has moved on (the reader's next push
+// is what lets the writer reach its next iteration), so one buffer per direction is enough.
+template <int EPL, int B>
+__device__ __forceinline__ void push_block(uint32_t slot_addr, uint32_t nslot_addr, const double (&col)[8][EPL],
+                                           const double (&nrm)[8], int lane) {
+#pragma unroll
+    for (int k = 0; k < EIG_C; ++k) {
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) dsmem_st(slot_addr + (uint32_t)((k * 32 * EPL + lane + 32 * e) * 8), col[B + k][e]);
+    }
+    if (lane < EIG_C) {
+        double v = nrm[B];
+        if (lane == 1) v = nrm[B + 1];
+        if (lane == 2) v = nrm[B + 2];
+        if (lane == 3) v = nrm[B + 3];
+        dsmem_st(nslot_addr + (uint32_t)(lane * 8), v);
+    }
+}
+template <int EPL, int B>
+__device__ __forceinline__ void take_block(const double (*slot)[32 * EPL], const double* nslot, double (&col)[8][EPL],
+                                           double (&nrm)[8], int lane) {
+#pragma unroll
+    for (int k = 0; k < EIG_C; ++k) {
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) col[B + k][e] = slot[k][lane + 32 * e];
+        nrm[B + k] = nslot[k];
+    }
+}
+
+template <int EPL, int FB, int SB>
+__device__ __forceinline__ void jacobi_iteration_p2p(EigSmem<EPL>& sm, double (&col)[8][EPL], double (&nrm)[8],
+                                                     double nmax, double& off, int w, int lw, int rank, int lane,
+                                                     int M, uint32_t parity) {
+    cross_blocks<EPL, FB, SB>(col, nrm, nmax, off, lane);
+    // SB (now at position 2w) meets position 2w-1 in warp w-1
+    if (w == 0) {
+        put_block<EPL, SB>(sm.park, sm.parkn, col, nrm, lane);
+        __syncwarp();
+    } else {
+        const int plw = (lw + EIG_WARPS - 1) % EIG_WARPS;
+        const int prk = (lw == 0) ? rank - 1 : rank;
+        push_block<EPL, SB>(dsmem_addr(&sm.slotA[plw][0][0], prk), dsmem_addr(&sm.normA[plw][0], prk), col, nrm, lane);
+        mbar_remote_arrive(dsmem_addr(&sm.fullA[plw], prk));
+    }
+    if (w + 1 < M) {
+        mbar_wait_cluster(&sm.fullA[lw], parity);
+        take_block<EPL, SB>(sm.slotA[lw], sm.normA[lw], col, nrm, lane);
+        cross_blocks<EPL, FB, SB>(col, nrm, nmax, off, lane);
+        // the neighbour's block stays at 2w+1, FB moves on to position 2w+2 (warp w+1)
+        const int nlw = (lw + 1) % EIG_WARPS;
+        const int nrk = (lw + 1 == EIG_WARPS) ? rank + 1 : rank;
+        push_block<EPL, FB>(dsmem_addr(&sm.slotB[nlw][0][0], nrk), dsmem_addr(&sm.normB[nlw][0], nrk), col, nrm, lane);
+        mbar_remote_arrive(dsmem_addr(&sm.fullB[nlw], nrk));
+    } else {
+#pragma unroll
+        for (int k = 0; k < EIG_C; ++k) {
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) col[SB + k][e] = col[FB + k][e];
+            nrm[SB + k] = nrm[FB + k];
+        }
+    }
+    if (w == 0) {
+        take_block<EPL, FB>(sm.park, sm.parkn, col, nrm, lane);
+        __syncwarp();
+    } else {
+        mbar_wait_cluster(&sm.fullB[lw], parity);
+        take_block<EPL, FB>(sm.slotB[lw], sm.normB[lw], col, nrm, lane);
+    }
+}
+
 // Grid = S * EPL CTAs, cluster = EPL CTAs, EIG_NT threads, dynamic smem = sizeof(EigSmem<EPL>).
-template <int EPL>
+template <int EPL, bool P2P>
 __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
     constexpr int N2 = 32 * EPL;
     constexpr int ELL = 16 * EPL;
@@ -282,6 +384,17 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
     const int q_head = sl.q_head, q_len = sl.q_len;
     const unsigned long long last_dump = sl.last_dump;
     const double thr = sl.error;
+    if (P2P) {
+        if (threadIdx.x == 0) {
+            for (int i = 0; i < EIG_WARPS; ++i) {
+                mbar_init_cta(&sm.fullA[i], 32);
+                mbar_init_cta(&sm.fullB[i], 32);
+            }
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        cluster_barrier();                      // every CTA's barriers exist before the first remote arrival
+    }
+    uint32_t itn = 0;
 
     // ---- load: columns 8w .. 8w+7 of the symmetrised, masked Gram -------------------
     const unsigned char* mk = A.mask + (size_t)s * ELL;
@@ -351,7 +464,10 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
         rot4<EPL, 0, 3, 1, 2, 4, 7, 5, 6>(col, nrm, nm, off, lane);
         // block pairs: 2M block positions, 2M rounds, two per iteration
 #pragma unroll 1
-        for (int it = 0; it < M; ++it) jacobi_iteration<EPL, 0, 4>(sm, col, nrm, nm, off, w, lw, rank, lane, M);
+        for (int it = 0; it < M; ++it, ++itn) {
+            if (P2P) jacobi_iteration_p2p<EPL, 0, 4>(sm, col, nrm, nm, off, w, lw, rank, lane, M, itn & 1u);
+            else jacobi_iteration<EPL, 0, 4>(sm, col, nrm, nm, off, w, lw, rank, lane, M);
+        }
         sweeps_done = sweep + 1;
     }
 
