@@ -13,8 +13,8 @@
 //   warp 1      UMMA issue: acc += hi.hi^T + hi.lo^T + lo.hi^T (kind::tf32, fp32 in TMEM)
 //   warps 2..   epilogue: tcgen05.ld the row of scores, scale by 1/||c_j||, running
 //               argmax (ties -> lowest j), threshold against ||x||, write label/score
-// MH = 2 (two accumulators, 256 rows per CTA) when the centroid slices leave room for
-// two pipeline stages, else MH = 1.
+// MH = accumulators (128 rows each) per CTA, NST = pipeline stages; the launcher picks the
+// deepest pipeline that fits the 227 KB of shared memory.
 #pragma once
 #include <float.h>
 #include "umma.cuh"
@@ -23,7 +23,6 @@ namespace mused {
 namespace atc {
 
 constexpr int KB = 32;                 // floats of K per step (one 128-byte swizzle row)
-constexpr int NST = 2;                 // pipeline stages
 
 struct Args {
     long long n;
@@ -34,7 +33,7 @@ struct Args {
     float* score;                      // nullable
 };
 
-template <int MH>
+template <int MH, int NST>
 struct Cfg {
     static constexpr int NTHREADS = 64 + MH * 128;
     static size_t stage_bytes(int NP) { return (size_t)MH * 2 * 128 * 128 + (size_t)2 * NP * 128; }
@@ -66,8 +65,8 @@ __global__ void k_assign_prep(const float* __restrict__ C, long long k, long lon
     }
 }
 
-template <int MH>
-__global__ void __launch_bounds__(Cfg<MH>::NTHREADS, 1)
+template <int MH, int NST>
+__global__ void __launch_bounds__(Cfg<MH, NST>::NTHREADS, 1)
 k_assign_tc(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_chi,
             const __grid_constant__ CUtensorMap tm_clo, Args A) {
     extern __shared__ unsigned char smem_dyn[];

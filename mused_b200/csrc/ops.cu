@@ -259,7 +259,7 @@ using namespace mused;
 extern "C" void mused_count_launches(uint64_t n);
 
 // tensor-core path of mused_assign (assign_tc.cuh); *done = false -> shape not eligible
-template <int MH>
+template <int MH, int NST>
 static int launch_assign_tc(const float* X, int64_t n, int64_t d, int64_t ld_x, int NP, const float* Chi,
                             const float* Clo, atc::Args& A, cudaStream_t st) {
     CUtensorMap tx, thi, tlo;
@@ -269,10 +269,10 @@ static int launch_assign_tc(const float* X, int64_t n, int64_t d, int64_t ld_x, 
         set_error("cuTensorMapEncodeTiled failed for the assignment operands");
         return MUSED_ERR_CUDA;
     }
-    const size_t smem = atc::Cfg<MH>::smem_bytes(NP);
-    MUSED_CUDA(cudaFuncSetAttribute(atc::k_assign_tc<MH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem = atc::Cfg<MH, NST>::smem_bytes(NP);
+    MUSED_CUDA(cudaFuncSetAttribute(atc::k_assign_tc<MH, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long tiles = (n + MH * 128 - 1) / (MH * 128);
-    atc::k_assign_tc<MH><<<(unsigned)tiles, atc::Cfg<MH>::NTHREADS, smem, st>>>(tx, thi, tlo, A);
+    atc::k_assign_tc<MH, NST><<<(unsigned)tiles, atc::Cfg<MH, NST>::NTHREADS, smem, st>>>(tx, thi, tlo, A);
     MUSED_CUDA(cudaGetLastError());
     return 0;
 }
@@ -300,9 +300,19 @@ int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float
         A.n = n; A.k = (int)k; A.NP = NP; A.kblocks = (int)(d / 32); A.metric = metric; A.tau = tau;
         A.cn2 = c2; A.labels = labels; A.score = score;
         const int sms = sm_count_of_current();
-        const bool two = atc::Cfg<2>::smem_bytes(NP) <= 227u * 1024u && (n + 255) / 256 >= sms;
-        int rc = two ? launch_assign_tc<2>(X, n, d, ld_x, NP, Chi, Clo, A, st)
-                     : launch_assign_tc<1>(X, n, d, ld_x, NP, Chi, Clo, A, st);
+        // tile shape (measured on B200, k = 150, d = 1024): two 128-row accumulators per CTA halve the
+        // centroid re-reads from L2 and win once every SM has a tile (2.43 TB/s at 1M rows against
+        // 2.08 TB/s); a window-sized call (10k rows) wants more, smaller CTAs with a deeper pipeline.
+        static int shape = -1;
+        if (shape < 0) shape = getenv("MUSED_ASSIGN_SHAPE") ? atoi(getenv("MUSED_ASSIGN_SHAPE")) : 0;
+        const size_t cap = 227u * 1024u;
+        const bool fits22 = atc::Cfg<2, 2>::smem_bytes(NP) <= cap;
+        const bool big = (n + 255) / 256 >= sms;
+        int rc;
+        if (fits22 && (shape == 22 || (shape == 0 && big))) rc = launch_assign_tc<2, 2>(X, n, d, ld_x, NP, Chi, Clo, A, st);
+        else if (shape != 12 && atc::Cfg<1, 4>::smem_bytes(NP) <= cap) rc = launch_assign_tc<1, 4>(X, n, d, ld_x, NP, Chi, Clo, A, st);
+        else if (shape != 12 && atc::Cfg<1, 3>::smem_bytes(NP) <= cap) rc = launch_assign_tc<1, 3>(X, n, d, ld_x, NP, Chi, Clo, A, st);
+        else rc = launch_assign_tc<1, 2>(X, n, d, ld_x, NP, Chi, Clo, A, st);
         MUSED_CUDA(cudaFreeAsync(Chi, st));
         MUSED_CUDA(cudaFreeAsync(Clo, st));
         MUSED_CUDA(cudaFreeAsync(c2, st));
