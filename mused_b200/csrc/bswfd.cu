@@ -51,6 +51,39 @@ __global__ void __launch_bounds__(256) k_bstage(const Tin* __restrict__ in, long
     }
 }
 
+// fp32 rows with 16-byte aligned, 4-divisible geometry: one WARP per row, 128-bit loads and stores
+// (the append is pure streaming: 4 bytes read and 8 written per element).  Same contract as
+// k_bstage: hi / lo planes and ||x||^2 in a fixed order (lane partials in element order, then the
+// xor tree) that does not depend on how the caller slices the stream.
+__global__ void __launch_bounds__(256) k_bstage_v4(const float* __restrict__ in, long long ld, long long d, long long m,
+                                                   int row_off, float* __restrict__ xhi, float* __restrict__ xlo,
+                                                   double* __restrict__ norm2) {
+    const int lane = threadIdx.x & 31;
+    const long long warps = (long long)gridDim.x * 8;
+    for (long long r = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); r < m; r += warps) {
+        const float4* src = reinterpret_cast<const float4*>(in + (size_t)r * ld);
+        float4* hi = reinterpret_cast<float4*>(xhi + (size_t)(row_off + r) * d);
+        float4* lo = reinterpret_cast<float4*>(xlo + (size_t)(row_off + r) * d);
+        double acc = 0.0;
+        for (long long c = lane; c < d / 4; c += 32) {
+            const float4 v = __ldcs(src + c);
+            float4 h, l;
+            umma::split_tf32(v.x, h.x, l.x);
+            umma::split_tf32(v.y, h.y, l.y);
+            umma::split_tf32(v.z, h.z, l.z);
+            umma::split_tf32(v.w, h.w, l.w);
+            hi[c] = h;
+            lo[c] = l;
+            acc = fma((double)v.x, (double)v.x, acc);
+            acc = fma((double)v.y, (double)v.y, acc);
+            acc = fma((double)v.z, (double)v.z, acc);
+            acc = fma((double)v.w, (double)v.w, acc);
+        }
+        acc = warp_sum(acc);
+        if (lane == 0) norm2[row_off + r] = acc;
+    }
+}
+
 // ---------------------------------------------------------------------------
 // K5: per-instance bookkeeping of one chunk (times t_a .. t_a + n - 1).
 // ---------------------------------------------------------------------------
@@ -87,7 +120,7 @@ __global__ void __launch_bounds__(256) k_bbook(BDev D, int n, unsigned long long
         unsigned long long last = sl.last_dump;
         const double thr = sl.error;
         for (int r = 0; r < n; ++r) {
-            if (D.norm2[r] >= thr) {               // :76-77 -> SlidingWindowFD.append (:56-80)
+            if (D.norm2[D.x0 + r] >= thr) {        // :76-77 -> SlidingWindowFD.append (:56-80)
                 if (len == D.capn) { head = (head + 1) % D.capn; --len; sl.overflow += 1; }
                 const int tail = (head + len) % D.capn;
                 qs[tail] = last;
@@ -123,8 +156,8 @@ __global__ void __launch_bounds__(256) k_bbook(BDev D, int n, unsigned long long
         for (int i = threadIdx.x; i < D.ell; i += 256) D.s2[(size_t)s * D.ell + i] = 0.0;
     }
     for (int k = 0; k < nr; ++k) {
-        const float* h = D.xhi + (size_t)raw_row[k] * D.d;
-        const float* l = D.xlo + (size_t)raw_row[k] * D.d;
+        const float* h = D.xhi + (size_t)(D.x0 + raw_row[k]) * D.d;
+        const float* l = D.xlo + (size_t)(D.x0 + raw_row[k]) * D.d;
         float* dst = D.ringV + ((size_t)s * D.capn + raw_slot[k]) * D.d;
         for (long long c = threadIdx.x; c < D.d; c += 256) dst[c] = h[c] + l[c];
     }
@@ -196,6 +229,8 @@ struct BEngine {
     CUtensorMap tr_t_hi, tr_t_lo, tr_sk_hi, tr_sk_lo, tr_x_hi, tr_x_lo; // K4 boxes
     unsigned char* raw = nullptr;     // H2D staging of caller rows
     size_t raw_bytes = 0;
+    long long sb_rows = 0;            // rows of the staging planes (+ ell of slack for the last TMA box)
+    long long ahead = 0;              // rows staged beyond the open chunk (inside one fit() call)
     QueryScratch Q;
     double *o_sketch = nullptr, *o_vt = nullptr, *o_s2 = nullptr, *o_delta = nullptr;
     std::vector<void*> allocs;
@@ -289,9 +324,11 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     A_(D.slots, Sa);
     A_(D.skhi, Sa * 2 * ell * d);
     A_(D.sklo, Sa * 2 * ell * d);
-    A_(D.xhi, (size_t)ell * d);
-    A_(D.xlo, (size_t)ell * d);
-    A_(D.norm2, (size_t)ell);
+    E->sb_rows = std::max<long long>(2 * ell, std::min<long long>(8192, (64ll << 20) / (d * 8)));
+    A_(D.xhi, (size_t)(E->sb_rows + ell) * d);
+    A_(D.xlo, (size_t)(E->sb_rows + ell) * d);
+    A_(D.norm2, (size_t)(E->sb_rows + ell));
+    D.x0 = 0;
     A_(D.mask, Sa * ell);
     A_(D.Gp, Sa * KS * D.n2 * D.n2);
     A_(D.G, Sa * D.n2 * D.n2);
@@ -339,8 +376,8 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     MUSED_CUDA(cudaMemcpy(D.slots, init.data(), sizeof(BSlot) * Sa, cudaMemcpyHostToDevice));
     CUresult r1 = encode_tmap_f32_2d(&E->tm_sk_hi, D.skhi, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
     CUresult r2 = encode_tmap_f32_2d(&E->tm_sk_lo, D.sklo, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
-    CUresult r3 = encode_tmap_f32_2d(&E->tm_x_hi, D.xhi, (uint64_t)ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
-    CUresult r4 = encode_tmap_f32_2d(&E->tm_x_lo, D.xlo, (uint64_t)ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
+    CUresult r3 = encode_tmap_f32_2d(&E->tm_x_hi, D.xhi, (uint64_t)(E->sb_rows + ell), (uint64_t)d, (uint64_t)d, (uint32_t)ell);
+    CUresult r4 = encode_tmap_f32_2d(&E->tm_x_lo, D.xlo, (uint64_t)(E->sb_rows + ell), (uint64_t)d, (uint64_t)d, (uint32_t)ell);
     {
         const uint32_t trows = (uint32_t)std::min<long long>(ell, 128), brows = (uint32_t)std::min<long long>(ell, 32);
         CUresult q[6];
@@ -348,8 +385,8 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
         q[1] = encode_tmap_f32_2d(&E->tr_t_lo, D.Tlo, (uint64_t)Sa * ell, (uint64_t)D.n2, (uint64_t)D.n2, trows);
         q[2] = encode_tmap_f32_2d(&E->tr_sk_hi, D.skhi, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, brows, 32, true);
         q[3] = encode_tmap_f32_2d(&E->tr_sk_lo, D.sklo, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, brows, 32, true);
-        q[4] = encode_tmap_f32_2d(&E->tr_x_hi, D.xhi, (uint64_t)ell, (uint64_t)d, (uint64_t)d, brows, 32, true);
-        q[5] = encode_tmap_f32_2d(&E->tr_x_lo, D.xlo, (uint64_t)ell, (uint64_t)d, (uint64_t)d, brows, 32, true);
+        q[4] = encode_tmap_f32_2d(&E->tr_x_hi, D.xhi, (uint64_t)(E->sb_rows + ell), (uint64_t)d, (uint64_t)d, brows, 32, true);
+        q[5] = encode_tmap_f32_2d(&E->tr_x_lo, D.xlo, (uint64_t)(E->sb_rows + ell), (uint64_t)d, (uint64_t)d, brows, 32, true);
         for (int i = 0; i < 6; ++i)
             if (q[i] != CUDA_SUCCESS) r1 = q[i];
     }
@@ -382,6 +419,7 @@ static int launch_gram(BEngine& E, cudaStream_t st) {
     A.ell = E.D.ell;
     A.KS = E.D.KS;
     A.kblocks = (int)(E.D.d / (32 * E.D.KS));
+    A.x0 = E.D.x0;
     k_gram_tc<N2><<<dim3(E.D.KS, E.D.S), 192, C::SMEM_BYTES, st>>>(E.tm_sk_hi, E.tm_sk_lo, E.tm_x_hi, E.tm_x_lo, A);
     MUSED_CUDA(cudaGetLastError());
     return 0;
@@ -414,6 +452,7 @@ static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t 
     A.ringS = E.D.ringS;
     A.ringT = E.D.ringT;
     A.tol = 1e-3;          // quadratic phase: the sweep that measures <= 1e-3 leaves ~1e-6 (Gram accuracy)
+    A.max_sweeps = 24;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(E.D.S * EPL));
     cfg.blockDim = dim3(EIG_NT);
@@ -492,6 +531,7 @@ int bengine_chunk_finish(BEngine* Ep, cudaStream_t st) {
     if (E.timing) { E.timed_chunks += 1; E.timed_rows += n; }
     E.done += (unsigned long long)n;
     E.pend = 0;
+    E.D.x0 += n;                       // the next chunk starts behind this one in the staging planes
     return 0;
 }
 
@@ -510,20 +550,50 @@ static long long chunk_room(const BEngine& E) {
     return cap - E.pend;
 }
 
-static int stage_rows(BEngine& E, const void* dev_rows, long long m, long long ld, int dtype, cudaStream_t st) {
+// K1 launch: m rows behind everything already staged.  logical = the rows join the open chunk at
+// once (phase API, one chunk at a time); otherwise they wait in the planes (fit() stages a whole
+// block of caller rows with ONE launch and then walks it chunk by chunk).
+static int stage_rows(BEngine& E, const void* dev_rows, long long m, long long ld, int dtype, bool logical,
+                      cudaStream_t st) {
     BDev& D = E.D;
+    if (E.pend == 0 && E.ahead == 0) D.x0 = 0;
+    const int row_off = D.x0 + E.pend + (int)E.ahead;
+    MUSED_REQUIRE(row_off + m <= E.sb_rows + D.ell, "internal: staging planes overflow (%d + %lld rows)", row_off, m);
     E.mark(0, st);
     switch (dtype) {
-        case MUSED_F64: k_bstage<double><<<(unsigned)m, 256, 0, st>>>((const double*)dev_rows, ld, D.d, E.pend, D.xhi, D.xlo, D.norm2); break;
-        case MUSED_F32: k_bstage<float><<<(unsigned)m, 256, 0, st>>>((const float*)dev_rows, ld, D.d, E.pend, D.xhi, D.xlo, D.norm2); break;
-        case MUSED_I64: k_bstage<long long><<<(unsigned)m, 256, 0, st>>>((const long long*)dev_rows, ld, D.d, E.pend, D.xhi, D.xlo, D.norm2); break;
-        case MUSED_I32: k_bstage<int><<<(unsigned)m, 256, 0, st>>>((const int*)dev_rows, ld, D.d, E.pend, D.xhi, D.xlo, D.norm2); break;
-        case MUSED_U8: k_bstage<unsigned char><<<(unsigned)m, 256, 0, st>>>((const unsigned char*)dev_rows, ld, D.d, E.pend, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_F64: k_bstage<double><<<(unsigned)m, 256, 0, st>>>((const double*)dev_rows, ld, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_F32:
+            if (D.d % 4 == 0 && ld % 4 == 0 && ((uintptr_t)dev_rows & 15) == 0)
+                k_bstage_v4<<<(unsigned)std::min<long long>((m + 7) / 8, 16ll * E.sm_count), 256, 0, st>>>(
+                    (const float*)dev_rows, ld, D.d, m, row_off, D.xhi, D.xlo, D.norm2);
+            else
+                k_bstage<float><<<(unsigned)m, 256, 0, st>>>((const float*)dev_rows, ld, D.d, row_off, D.xhi, D.xlo, D.norm2);
+            break;
+        case MUSED_I64: k_bstage<long long><<<(unsigned)m, 256, 0, st>>>((const long long*)dev_rows, ld, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_I32: k_bstage<int><<<(unsigned)m, 256, 0, st>>>((const int*)dev_rows, ld, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_U8: k_bstage<unsigned char><<<(unsigned)m, 256, 0, st>>>((const unsigned char*)dev_rows, ld, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
     }
     MUSED_CUDA(cudaGetLastError());
     E.mark(0, st);
     mused_count_launches(1);
-    E.pend += (int)m;
+    if (logical) E.pend += (int)m;
+    else E.ahead += m;
+    return 0;
+}
+
+// the open chunk back to row 0 of the staging planes (rare: only when a fit() call finds the planes
+// nearly full behind a partial chunk)
+static int compact_open_chunk(BEngine& E, cudaStream_t st) {
+    BDev& D = E.D;
+    if (D.x0 == 0) return 0;
+    if (E.pend > 0) {
+        MUSED_REQUIRE(D.x0 >= E.pend, "internal: open chunk overlaps its destination");
+        const size_t bytes = (size_t)E.pend * D.d * sizeof(float);
+        MUSED_CUDA(cudaMemcpyAsync(D.xhi, D.xhi + (size_t)D.x0 * D.d, bytes, cudaMemcpyDeviceToDevice, st));
+        MUSED_CUDA(cudaMemcpyAsync(D.xlo, D.xlo + (size_t)D.x0 * D.d, bytes, cudaMemcpyDeviceToDevice, st));
+        MUSED_CUDA(cudaMemcpyAsync(D.norm2, D.norm2 + D.x0, (size_t)E.pend * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    }
+    D.x0 = 0;
     return 0;
 }
 
@@ -553,14 +623,27 @@ int bengine_fit(BEngine* Ep, const void* rows, long long n_rows, long long ld, i
         }
         long long off = 0;
         while (off < blk) {
-            const long long m = std::min(blk - off, chunk_room(E));
-            int rc = stage_rows(E, (const char*)dev + (size_t)off * dev_ld * es, m, dev_ld, dtype, st);
+            // stage as many of the block's rows as the planes take, in one launch ...
+            long long space = E.sb_rows - (E.D.x0 + E.pend);
+            if (space < std::min<long long>(blk - off, E.D.ell)) {
+                int rc = compact_open_chunk(E, st);
+                if (rc) return rc;
+                space = E.sb_rows - E.pend;
+            }
+            const long long m = std::min(blk - off, space);
+            int rc = stage_rows(E, (const char*)dev + (size_t)off * dev_ld * es, m, dev_ld, dtype, false, st);
             if (rc) return rc;
             off += m;
-            E.time += (unsigned long long)m;
-            if (chunk_room(E) == 0) {
-                rc = process_chunk(E, st);
-                if (rc) return rc;
+            // ... then fold them chunk by chunk
+            while (E.ahead > 0) {
+                const long long take = std::min(E.ahead, chunk_room(E));
+                E.pend += (int)take;
+                E.ahead -= take;
+                E.time += (unsigned long long)take;
+                if (chunk_room(E) == 0) {
+                    rc = process_chunk(E, st);
+                    if (rc) return rc;
+                }
             }
         }
         fed += blk;
@@ -720,7 +803,7 @@ int bengine_stage(BEngine* Ep, const void* rows, long long m, long long ld, int 
         dev = E.raw;
         dev_ld = E.D.d;
     }
-    int rc = stage_rows(E, dev, m, dev_ld, dtype, st);
+    int rc = stage_rows(E, dev, m, dev_ld, dtype, true, st);
     if (rc) return rc;
     E.time += (unsigned long long)m;
     if (where == MUSED_HOST) MUSED_CUDA(cudaStreamSynchronize(st));

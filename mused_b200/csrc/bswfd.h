@@ -9,14 +9,15 @@ namespace mused {
 constexpr int BS_MAX_ELL = 128;
 
 struct BDev {
-    int S, ell, n2, capn, KS, pad;
+    int S, ell, n2, capn, KS;
+    int x0;                    // row of the staging planes where the open chunk starts
     long long d;
     unsigned long long N;
     double qcap;
     BSlot* slots;
     float *skhi, *sklo;        // [S][2][ell][d] sketch planes (TF32 hi / lo), ping-pong
-    float *xhi, *xlo;          // [ell][d] the chunk being assembled / processed
-    double* norm2;             // [ell]
+    float *xhi, *xlo;          // [stage rows + ell][d] staged rows of a fit() call; the open chunk starts at row x0
+    double* norm2;             // [stage rows + ell] ||x||^2 of the staged rows
     unsigned char* mask;       // [S][ell] 1 = chunk row is a raw snapshot at this instance's level
     float* Gp;                 // [S][KS][n2][n2] split-K partials of K2
     double* G;                 // [S][n2][n2] their float64 sum (the buffer a column-sharded run allreduces)

@@ -26,6 +26,7 @@ struct GramArgs {
     const BSlot* slots;   // cur plane per instance
     float* Gp;            // [S][KS][n2][n2]
     int ell, KS, kblocks; // kblocks = k-blocks of 32 floats per CTA
+    int x0;               // first row of the open chunk in the staging planes
 };
 
 template <int N2>
@@ -85,9 +86,9 @@ k_gram_tc(const __grid_constant__ CUtensorMap tm_sk_hi, const __grid_constant__ 
                 const int col = (ks * A.kblocks + kb) * 32;
                 umma::mbar_expect_tx(&full[st], 2 * N2 * 128);
                 umma::tma_load_2d(hi, &tm_sk_hi, &full[st], col, row_sk);
-                umma::tma_load_2d(hi + ELL * 128, &tm_x_hi, &full[st], col, 0);
+                umma::tma_load_2d(hi + ELL * 128, &tm_x_hi, &full[st], col, A.x0);
                 umma::tma_load_2d(lo, &tm_sk_lo, &full[st], col, row_sk);
-                umma::tma_load_2d(lo + ELL * 128, &tm_x_lo, &full[st], col, 0);
+                umma::tma_load_2d(lo + ELL * 128, &tm_x_lo, &full[st], col, A.x0);
             }
         }
     } else if (warp == 1) {

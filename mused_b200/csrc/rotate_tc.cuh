@@ -96,8 +96,8 @@ k_rotate_tc(const __grid_constant__ CUtensorMap tm_t_hi, const __grid_constant__
                             umma::tma_load_2d(b_hi + off, &tm_sk_hi, &full[st], c0 + ch * 32, row_sk + k);
                             umma::tma_load_2d(b_lo + off, &tm_sk_lo, &full[st], c0 + ch * 32, row_sk + k);
                         } else {
-                            umma::tma_load_2d(b_hi + off, &tm_x_hi, &full[st], c0 + ch * 32, k - ell);
-                            umma::tma_load_2d(b_lo + off, &tm_x_lo, &full[st], c0 + ch * 32, k - ell);
+                            umma::tma_load_2d(b_hi + off, &tm_x_hi, &full[st], c0 + ch * 32, D.x0 + k - ell);
+                            umma::tma_load_2d(b_lo + off, &tm_x_lo, &full[st], c0 + ch * 32, D.x0 + k - ell);
                         }
                     }
                 }
