@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--cpu-rows", type=int, default=0, help="rows of the cpu_baseline sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--phase-times", action="store_true", help="diagnostic: synchronise after assign and print fit/get/assign wall ms")
     ap.add_argument("--schedule", default="batched", choices=["batched", "reference"],
                     help="batched: north_star's chunked tensor-core schedule (headline); "
                          "reference: the reference's per-row flush schedule")
@@ -259,11 +260,22 @@ def run_ours(args, rank, local_rank, world):
         """`value`: whole windows (fit + get + assign) with inputs resident in HBM."""
         sk = SeqBasedSWFD(WIN, R, D, ELL, device=local_rank, cluster=args.cluster, schedule=schedule)
 
+        get_s = [0.0, 0.0, 0.0]                             # host wall seconds: get, fit (to sync), assign
+
         def step(i):
             blk = Ad[i * WIN:(i + 1) * WIN]
+            tf = time.perf_counter()
             sk.fit(blk)
+            torch.cuda.current_stream().synchronize()      # get() starts with this wait; time it apart
+            tg = time.perf_counter()
             out = sk.get()
+            ta = time.perf_counter()
             lab = mo.cosine_assign(blk, Cd, TAU, device=dev)
+            if args.phase_times:
+                torch.cuda.current_stream().synchronize()
+            get_s[0] += ta - tg
+            get_s[1] += tg - tf
+            get_s[2] += time.perf_counter() - ta
             return out, lab
 
         for i in range(warmup):
@@ -277,6 +289,7 @@ def run_ours(args, rank, local_rank, world):
         else:
             sk.kernel_timing(enable=1)
         l0 = lib.mused_launch_count()
+        get_s[0] = get_s[1] = get_s[2] = 0.0
         e0.record()
         for i in range(warmup, warmup + steps):
             out, lab = step(i)
@@ -285,9 +298,11 @@ def run_ours(args, rank, local_rank, world):
         ms_total = max_over_ranks(e0.elapsed_time(e1))
         res = {"ms_total": ms_total, "launches": int(lib.mused_launch_count() - l0),
                "value": world * steps * WIN / (ms_total * 1e-3), "sketch": out[0],
+               "get_ms": 1e3 * get_s[0] / steps, "fit_ms": 1e3 * get_s[1] / steps, "assign_ms": 1e3 * get_s[2] / steps,
                "clocks": sampler.stop() if (sample_clocks and rank == 0) else None}
         if schedule == "batched":
             res["kernel_ms"], res["chunks"], res["k_rows"] = sk.kernel_ms(enable=0)
+            res["gaps_ms"] = sk.kernel_gaps()
         else:
             res["k_ms"], res["k_launches"], res["k_rows"] = sk.kernel_timing(enable=0)
             res["prof"] = sk.profile()
@@ -310,10 +325,15 @@ def run_ours(args, rank, local_rank, world):
         sk2 = SeqBasedSWFD(WIN, R, D, ELL, device=local_rank, cluster=args.cluster, schedule=args.schedule)
         lab_host = torch.empty(WIN, dtype=torch.int32).pin_memory()
 
+        get2_s = [0.0]
+
         def step_e2e(i):
             blk = An[i * WIN:(i + 1) * WIN]
             sk2.fit(blk)                                   # H2D inside the C-ABI call
+            torch.cuda.current_stream().synchronize()
+            tg = time.perf_counter()
             out = sk2.get()                                # sketch / sigma^2 / Vt D2H inside
+            get2_s[0] += time.perf_counter() - tg
             xd = Ah[i * WIN:(i + 1) * WIN].to(dev, non_blocking=True)
             lab = mo.cosine_assign(xd, Cd, TAU, device=dev)
             lab_host.copy_(lab, non_blocking=True)
@@ -324,6 +344,7 @@ def run_ours(args, rank, local_rank, world):
             step_e2e(i)
         barrier()
         t0 = time.perf_counter()
+        get2_s[0] = 0.0
         e0.record()
         for i in range(args.warmup, n_steps):
             step_e2e(i)
@@ -333,7 +354,7 @@ def run_ours(args, rank, local_rank, world):
         e2e = {"value": world * args.steps * WIN / (ms_e2e * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": 2 * WIN * D * 4,      # rows for fit + rows for assign
                "d2h_bytes_per_step": 2 * ELL * D * 8 + ELL * 8 + 8 + WIN * 4,
-               "wall_s": time.perf_counter() - t0}
+               "wall_s": time.perf_counter() - t0, "get_ms_per_step": 1e3 * get2_s[0] / args.steps}
         sk2.close()
     del Ad
 
@@ -384,6 +405,9 @@ def run_ours(args, rank, local_rank, world):
                           "issued_TFLOPs_3xTF32": 3 * S * 2.0 * ELL * n2 * D / (us["K4_rotate"] * 1e-6) / 1e12,
                           "peak_bf16_TFLOPs": tpeak},
             "K5_book": {"us_per_chunk": us["K5_book"]},
+            "stream_idle": {"us_per_chunk_inside": main_res["gaps_ms"][0] / chunks * 1e3,
+                            "us_per_chunk_between": main_res["gaps_ms"][1] / chunks * 1e3,
+                            "note": "CUDA-event time between the end of one kernel and the start of the next"},
         }
     elif main_res.get("k_launches"):
         rows_per_launch = main_res["k_rows"] / main_res["k_launches"]
@@ -424,7 +448,8 @@ def run_ours(args, rank, local_rank, world):
                    "l2": "each step streams a fresh 41 MB window (> nothing cached from the previous step's rows); "
                          "FD state is meant to stay L2-resident",
                    "query_level": main_res["level"]},
-        "clocks": main_res["clocks"], "e2e": e2e, "gpu_launches": main_res["launches"], "roofline": roofline,
+        "clocks": main_res["clocks"], "get_ms_per_step": main_res["get_ms"],
+        "fit_ms_per_step": main_res["fit_ms"], "assign_ms_per_step": main_res["assign_ms"] if args.phase_times else None, "e2e": e2e, "gpu_launches": main_res["launches"], "roofline": roofline,
         "cpu_baseline": cpu, "cov_error": cov,
         "flushes_per_row": sum(o["n_flush"] for o in st) / float(n_steps * WIN),
     }

@@ -122,6 +122,9 @@ int mused_swfd_timing(mused_swfd_t* h, int enable, double* ms, int64_t* launches
  * ms5 = {K1 stage, K5 bookkeeping, K2 Gram, K3 eigensolve, K4 rotate}; chunks and rows
  * folded meanwhile.  enable as in mused_swfd_timing. */
 int mused_swfd_kernel_ms(mused_swfd_t* h, int enable, double* ms5, int64_t* chunks, int64_t* rows);
+/* Stream idle time (ms) of the period closed by the last mused_swfd_kernel_ms(enable >= 0):
+ * gaps2[0] between the kernels of a chunk, gaps2[1] between consecutive chunks of one fit. */
+int mused_swfd_kernel_gaps(mused_swfd_t* h, double* gaps2);
 /* SM cycles the per-row kernel spent per phase, per physical FD instance:
  * cycles[inst * 16 + k], k = {A bookkeeping, B gemv, C Q^T g, D deflate, E secular roots,
  * F coupling vector, G eigenvector rows, H eigenvector GEMM, flush, dump, raw, rows} */
@@ -226,7 +229,9 @@ int mused_contingency(const int32_t* prev, const int32_t* cur, int64_t n, int32_
  * sqrt(evals), left singular vectors = vecs).  G: n x n float64 device, leading
  * dimension ld; evals (n, descending) and vecs (n x n, ROW i = eigenvector i,
  * leading dimension ld_vecs) are device buffers.  Whole-GPU one-sided block
- * Jacobi (csrc/eig_big.cuh); n up to ~1750 on a 148-SM B200.  Synchronises
+ * Jacobi (csrc/eig_big.cuh); n up to ~1750 on a 148-SM B200.  Eigenvectors of
+ * eigenvalues at round-off level (<= 1e-10 of the largest) are returned as
+ * zero rows: their direction is numerical noise.  Synchronises
  * the stream.  *sweeps (nullable) = Jacobi sweeps taken. */
 int mused_sym_eig(const double* G, int64_t n, int64_t ld, double* evals, double* vecs,
                   int64_t ld_vecs, int32_t* sweeps, void* stream);

@@ -45,7 +45,7 @@ SYMBOLS = [
     "mused_fd_create", "mused_fd_destroy", "mused_fd_fit", "mused_fd_fit_batches",
     "mused_fd_dump", "mused_fd_flush", "mused_fd_get",
     "mused_assign", "mused_topk_adjacency", "mused_contingency", "mused_sym_eig",
-    "mused_topk_adjacency_f64",
+    "mused_topk_adjacency_f64", "mused_swfd_kernel_gaps",
 ]
 
 
@@ -66,6 +66,7 @@ def load():
     lib.mused_swfd_profile.argtypes = [vp, vp, i64]
     lib.mused_swfd_timing.argtypes = [vp, C.c_int, C.POINTER(dbl), C.POINTER(i64), C.POINTER(i64)]
     lib.mused_swfd_kernel_ms.argtypes = [vp, C.c_int, C.POINTER(dbl), C.POINTER(i64), C.POINTER(i64)]
+    lib.mused_swfd_kernel_gaps.argtypes = [vp, C.POINTER(dbl)]
     lib.mused_swfd_chunk_room.argtypes = [vp, C.POINTER(i64), C.POINTER(i64)]
     lib.mused_swfd_stage.argtypes = [vp, vp, i64, i64, C.c_int, C.c_int, vp]
     lib.mused_swfd_chunk_gram.argtypes = [vp, vp]

@@ -239,6 +239,8 @@ struct BEngine {
     bool timing = false;
     std::vector<cudaEvent_t> ev[5];
     double timed_ms[5] = {0, 0, 0, 0, 0};
+    double gap_last[2] = {0, 0};
+    double gap_ms[2] = {0, 0};        // GPU idle between the kernels of a chunk / between chunks of one fit()
     long long timed_chunks = 0, timed_rows = 0;
 
     template <class T>
@@ -317,6 +319,10 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     // split-K: enough CTAs to cover the SMs, K slices of whole 32-float blocks
     int KS = 16;
     while (KS > 1 && (d % (32 * KS) != 0 || (long long)S * KS > 2LL * E->sm_count)) KS >>= 1;
+    if (getenv("MUSED_GRAM_KS")) {
+        const int want = atoi(getenv("MUSED_GRAM_KS"));
+        if (want >= 1 && want <= 16 && d % (32 * want) == 0) KS = want;
+    }
     D.KS = KS;
     int rc = 0;
 #define A_(p, n) if ((rc = E->alloc(&(p), (n))) != 0) { delete E; return rc; }
@@ -849,6 +855,24 @@ int bengine_debug(BEngine* Ep, double* scal, double* sigma2, unsigned long long*
 int bengine_timing(BEngine* Ep, int enable, double* ms, long long* chunks, long long* rows) {
     BEngine& E = *Ep;
     MUSED_CUDA(cudaSetDevice(E.device));
+    {
+        // idle time on the stream: end mark of one kernel class -> start mark of the next (nothing
+        // is enqueued in between), chunk by chunk; rotate -> next bookkeeping counts as the
+        // inter-chunk gap unless a get() sits in between (> 5 ms)
+        const size_t nc = std::min(std::min(E.ev[1].size(), E.ev[2].size()), std::min(E.ev[3].size(), E.ev[4].size())) / 2;
+        for (size_t c = 0; c < nc; ++c) {
+            float t = 0.f;
+            MUSED_CUDA(cudaEventSynchronize(E.ev[4][2 * c + 1]));
+            for (int k = 1; k < 4; ++k) {
+                MUSED_CUDA(cudaEventElapsedTime(&t, E.ev[k][2 * c + 1], E.ev[k + 1][2 * c]));
+                E.gap_ms[0] += t;
+            }
+            if (c + 1 < nc) {
+                MUSED_CUDA(cudaEventElapsedTime(&t, E.ev[4][2 * c + 1], E.ev[1][2 * c + 2]));
+                if (t < 5.f) E.gap_ms[1] += t;
+            }
+        }
+    }
     for (int k = 0; k < 5; ++k) {
         for (size_t i = 0; i + 1 < E.ev[k].size(); i += 2) {
             float t = 0.f;
@@ -865,9 +889,18 @@ int bengine_timing(BEngine* Ep, int enable, double* ms, long long* chunks, long 
     if (enable >= 0) {
         E.timing = enable != 0;
         for (int k = 0; k < 5; ++k) E.timed_ms[k] = 0.0;
+        E.gap_last[0] = E.gap_ms[0];
+        E.gap_last[1] = E.gap_ms[1];
+        E.gap_ms[0] = E.gap_ms[1] = 0.0;
         E.timed_chunks = 0;
         E.timed_rows = 0;
     }
+    return 0;
+}
+
+int bengine_gaps(BEngine* E, double* gaps2) {
+    gaps2[0] = E->gap_last[0];
+    gaps2[1] = E->gap_last[1];
     return 0;
 }
 

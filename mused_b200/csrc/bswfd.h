@@ -45,6 +45,9 @@ int bengine_debug(BEngine* E, double* scal, double* sigma2, unsigned long long* 
 // CUDA-event time per kernel class since the last reset: ms[5] = {stage, book, gram, eig, rotate},
 // chunks processed.  enable: 1 arm+reset, 0 disarm+reset, -1 read only.
 int bengine_timing(BEngine* E, int enable, double* ms, long long* chunks, long long* rows);
+// GPU idle time of the period closed by the last bengine_timing(enable >= 0): ms between the kernels
+// of a chunk, ms between consecutive chunks of one fit()
+int bengine_gaps(BEngine* E, double* gaps2);
 
 // Phase API for the column-sharded mode (mused_b200/sharded.py drives it; the two
 // exchange points of SURVEY 8(e) sit between the phases):

@@ -409,10 +409,14 @@ __global__ void __launch_bounds__(NT, 1) k_eig_big(Args A) {
     // ---- eigenvalues = column norms, eigenvectors = normalised columns -------------------
     block_gram<CB>(W, nr, S, part, tid);
     const bool bad = __ldcg(A.info + 1) != 0;
+    // A column whose norm sank to round-off level (lambda <= 1e-10 lambda_max) is noise, not a
+    // direction: its eigenvalue is kept, its eigenvector is returned as a ZERO row so that a caller
+    // that projects onto it (vt = M^T v / sqrt(lambda)) gets nothing instead of amplified noise.
+    const double lam_floor = 1e-10 * sqrt(fmax(nmax, 0.0));
     for (int i = 0; i < M; ++i) {
         const double lam = sqrt(fmax(S[i * M + i], 0.0));
         const int slot = 2 * p * CB + i;
-        const double inv = lam > 0.0 ? 1.0 / lam : 0.0;
+        const double inv = (lam > lam_floor && lam > 0.0) ? 1.0 / lam : 0.0;
         if (tid == 0) A.lam[slot] = bad ? __longlong_as_double(0x7ff8000000000000ll) : lam;
         for (int r = tid; r < nr; r += NT) A.VT[(size_t)slot * A.ldt + r] = W[i * nr + r] * inv;
     }

@@ -247,6 +247,21 @@ __global__ void k_contingency(const int* __restrict__ prev, const int* __restric
     }
 }
 
+// Scratch comes from the stream-ordered pool; by default that pool hands its memory back to the
+// driver at every synchronisation, which makes the next cudaMallocAsync map fresh pages (slow and
+// erratic).  Keep the pages: one attribute on the device's default pool, set once per device.
+static void keep_pool_memory() {
+    static bool done[64] = {false};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64 || done[dev]) return;
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+        unsigned long long keep = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+    done[dev] = true;
+}
+
 static int sm_count_of_current() {
     int dev = 0, n = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
@@ -286,6 +301,7 @@ int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float
     MUSED_REQUIRE(metric == MUSED_METRIC_COSINE || metric == MUSED_METRIC_L2, "unknown metric %d", metric);
     if (n == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
+    keep_pool_memory();
     // tensor-core path: K in whole 128-byte rows, every centroid in one UMMA N, TMA-addressable X
     const int NP = (int)((k + 15) / 16 * 16);
     if (d % 32 == 0 && k <= 256 && ld_x % 4 == 0 && ((uintptr_t)X & 15) == 0 && n < (1ll << 31) &&
@@ -341,6 +357,7 @@ int mused_topk_adjacency(const float* feats, int64_t W, int64_t f, int64_t ld, i
     MUSED_REQUIRE(W * 4 <= 200 * 1024, "window of %lld rows exceeds the per-row shared-memory select (max 51200)", (long long)W);
     if (k == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
+    keep_pool_memory();
     float *n2 = nullptr, *S = nullptr;
     MUSED_CUDA(cudaMallocAsync((void**)&n2, sizeof(float) * (size_t)W, st));
     MUSED_CUDA(cudaMallocAsync((void**)&S, sizeof(float) * (size_t)W * W, st));
@@ -369,6 +386,7 @@ int mused_topk_adjacency_f64(const double* feats, int64_t W, int64_t f, int64_t 
     MUSED_REQUIRE(W * 8 <= 200 * 1024, "window of %lld rows exceeds the per-row shared-memory select (max 25600)", (long long)W);
     if (k == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
+    keep_pool_memory();
     double* S = nullptr;
     MUSED_CUDA(cudaMallocAsync((void**)&S, sizeof(double) * (size_t)W * W, st));
     const int sms = sm_count_of_current();

@@ -882,6 +882,10 @@ int mused_swfd_timing(mused_swfd_t* h, int enable, double* ms, int64_t* launches
     }
     return 0;
 }
+int mused_swfd_kernel_gaps(mused_swfd_t* h, double* gaps2) {
+    MUSED_REQUIRE(h && h->B && gaps2, "mused_swfd_kernel_gaps needs a schedule=batched handle");
+    return bengine_gaps(h->B, gaps2);
+}
 int mused_swfd_kernel_ms(mused_swfd_t* h, int enable, double* ms5, int64_t* chunks, int64_t* rows) {
     MUSED_REQUIRE(h && h->B, "mused_swfd_kernel_ms needs a schedule=batched handle");
     long long c = 0, r = 0;

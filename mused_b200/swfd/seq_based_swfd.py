@@ -145,6 +145,13 @@ class SeqBasedSWFD:
         _lib.check(self._lib.mused_swfd_kernel_ms(self._h, int(enable), ms, C.byref(nc), C.byref(nr)))
         return dict(zip(self.KERNELS, (float(v) for v in ms))), int(nc.value), int(nr.value)
 
+    def kernel_gaps(self):
+        """schedule="batched": stream idle ms (inside chunks, between chunks) of the period closed
+        by the last ``kernel_ms(enable >= 0)``."""
+        g = (C.c_double * 2)()
+        _lib.check(self._lib.mused_swfd_kernel_gaps(self._h, g))
+        return float(g[0]), float(g[1])
+
     def close(self):
         if getattr(self, "_h", None) is not None and self._h.value:
             self._lib.mused_swfd_destroy(self._h)

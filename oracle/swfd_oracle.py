@@ -137,8 +137,11 @@ class Level:
         self.d, self.ell = d, ell
         self.time = np.uint64(0)
 
-    def _tick(self):                                      # :60-75 / :90-107
-        self.time += np.uint64(1)
+    def _tick(self, t=None):                              # :60-75 / :90-107
+        if t is not None:                                 # explicit arrival time (TimeBasedSWFD)
+            self.time = np.uint64(t)
+        else:
+            self.time += np.uint64(1)
         while self.period < self.time // self.N:
             self.fd = self.aux
             self.aux = _Side(self.d, self.ell, self.error, last_dump_time=self.time)
@@ -149,13 +152,13 @@ class Level:
         side.last_dump_time = self.time + 1
         side.queue.append((v, s, self.time))
 
-    def append(self, X):                                  # :56-80 raw-row snapshot
-        self._tick()
+    def append(self, X, t=None):                          # :56-80 raw-row snapshot
+        self._tick(t)
         self._push(self.fd, X)
         self._push(self.aux, X)
 
-    def fit(self, X):                                     # :83-138
-        self._tick()
+    def fit(self, X, t=None):                             # :83-138
+        self._tick(t)
         for side in (self.fd, self.aux):                  # :109-121
             q = side.queue
             while len(q) != 0 and q[0][2] + self.N <= self.time:
@@ -246,6 +249,43 @@ class SeqSWFD:
                     last_dump_time=int(side.last_dump_time),
                     q_s=[int(e[1]) for e in side.queue], q_t=[int(e[2]) for e in side.queue]))
         return out
+
+
+class TimeSWFD(SeqSWFD):
+    """seq_based_swfd.py:106-207 TimeBasedSWFD(N, R, d, sketch_dim, beta=4, **kw): rows carry an
+    explicit arrival time, the ladder has ceil(log2(N R / l)) levels with thresholds 2^j."""
+
+    def __init__(self, N, R, d, sketch_dim, beta=4.0, **kwargs):
+        self.N = np.uint64(N)
+        self.d, self.R, self.beta, self.ell = d, R, beta, sketch_dim
+        self.logR = int(np.ceil(np.log2(N * R / sketch_dim)))                      # :120
+        self.levels = {}
+        if "upper_F_norm" in kwargs:                                               # :131-141
+            self.logR = int(np.ceil(np.log2(kwargs["upper_F_norm"] / self.ell)))
+            base = 1.0
+            if "lower_F_norm" in kwargs:
+                self.logR = int(np.ceil(np.log2(kwargs["upper_F_norm"] / kwargs["lower_F_norm"])))
+                base = kwargs["lower_F_norm"] / self.ell
+            for j in range(self.logR):
+                self.levels[j] = Level(self.N, d, self.ell, error=base * (2 ** j))
+        else:                                                                      # :143-146
+            for j in range(self.logR):
+                self.levels[j] = Level(self.N, d, self.ell, error=2 ** j)
+        self.time = np.uint64(0)
+
+    def fit(self, X, t):                                                           # :150-189
+        self.time = t
+        cap = (2 + 8 / self.beta) * self.ell
+        for j in range(self.logR):
+            lv = self.levels[j]
+            for side in (lv.fd, lv.aux):
+                q = side.queue
+                while len(q) != 0 and (len(q) > cap or q[0][2] + self.N <= self.time):
+                    q.popleft()
+            if X @ X.T >= lv.aux.C.error:                                          # :185-186
+                lv.append(X, t)
+            else:
+                lv.fit(X, t)
 
 
 def cov_error(A_w, B):
