@@ -377,12 +377,13 @@ def run_ours(args, rank, local_rank, world):
         achieved = bytes_per_row * rows_per_launch / dur_s / 1e9
         # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full of this workload
         # (profiles/r01_ncu_full_summary.csv); the FD state is L2-resident, hence far below the algorithmic bytes
-        ncu_traffic = {"K3_eig": 6377728, "K2_gram": 13857280 + 2824704, "K1_stage": 526080, "K5_book": 126720}
+        ncu_traffic = {"K3_eig": 6378240, "K2_gram": 13872640 + 1511680, "K1_stage": 33566976 + 11879680,
+                       "K5_book": 127232, "K4_rotate": 16892416 + 84224}
         roofline = {"bound": "hbm", "kernel": {"K1_stage": "k_bstage", "K5_book": "k_bbook", "K2_gram": "k_gram_tc",
                                                 "K3_eig": "k_eig_jacobi", "K4_rotate": "k_rotate_tc"}[dom],
                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": ncu_traffic.get(dom),
-                    "fp64_pipe_active_pct": 30.4 if dom == "K3_eig" else None,
+                    "fp64_pipe_active_pct": 30.7 if dom == "K3_eig" else None,
                     "peak_source": how, "algorithmic_bytes_per_row": bytes_per_row,
                     "rows_per_launch": rows_per_launch, "avg_launch_ms": km[dom] / chunks,
                     "share_of_step": km[dom] / main_res["ms_total"],
