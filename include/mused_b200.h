@@ -92,6 +92,13 @@ int mused_swfd_destroy(mused_swfd_t* h);
 int mused_swfd_fit(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld,
                    int dtype, int where, void* stream);
 
+/* TimeBasedSWFD.fit(X, t) (swfd/seq_based_swfd.py:150-189): the same per-row rules with an
+ * explicit arrival time per row instead of the running counter; times[r] (HOST array of n_rows
+ * values, non-decreasing) may repeat or skip whole windows (then both sides of a level start over,
+ * sliding_windows_frequent_directions.py:66-75).  schedule = reference only. */
+int mused_swfd_fit_timed(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld,
+                         int dtype, int where, const uint64_t* times, void* stream);
+
 /* SeqBasedSWFD.get (seq_based_swfd.py:83-100 -> sliding_windows_...py:154-173).
  * Like the reference it flushes the chosen level's pending rows (a state
  * mutation).  sketch: ell x d, sigma2: ell, vt: ell x d (may be NULL),

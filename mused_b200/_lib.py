@@ -45,7 +45,7 @@ SYMBOLS = [
     "mused_fd_create", "mused_fd_destroy", "mused_fd_fit", "mused_fd_fit_batches",
     "mused_fd_dump", "mused_fd_flush", "mused_fd_get",
     "mused_assign", "mused_topk_adjacency", "mused_contingency", "mused_sym_eig",
-    "mused_topk_adjacency_f64", "mused_swfd_kernel_gaps",
+    "mused_topk_adjacency_f64", "mused_swfd_kernel_gaps", "mused_swfd_fit_timed",
 ]
 
 
@@ -78,6 +78,7 @@ def load():
     lib.mused_swfd_create.argtypes = [C.POINTER(vp), C.POINTER(SwfdCfg)]
     lib.mused_swfd_destroy.argtypes = [vp]
     lib.mused_swfd_fit.argtypes = [vp, vp, i64, i64, C.c_int, C.c_int, vp]
+    lib.mused_swfd_fit_timed.argtypes = [vp, vp, i64, i64, C.c_int, C.c_int, vp, vp]
     lib.mused_swfd_get.argtypes = [vp, vp, vp, vp, C.POINTER(dbl), C.POINTER(i32), C.c_int, vp]
     lib.mused_swfd_size.argtypes = [vp, C.POINTER(i64)]
     lib.mused_swfd_time.argtypes = [vp, C.POINTER(C.c_uint64)]

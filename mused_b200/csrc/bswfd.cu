@@ -318,7 +318,7 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     D.capn = (int)floor(D.qcap) + (int)batch + (int)ell + 2;
     // split-K: enough CTAs to cover the SMs, K slices of whole 32-float blocks
     int KS = 16;
-    while (KS > 1 && (d % (32 * KS) != 0 || (long long)S * KS > 2LL * E->sm_count)) KS >>= 1;
+    while (KS > 1 && (d % (32 * KS) != 0 || (long long)S * KS > 1LL * E->sm_count)) KS >>= 1;
     if (getenv("MUSED_GRAM_KS")) {
         const int want = atoi(getenv("MUSED_GRAM_KS"));
         if (want >= 1 && want <= 16 && d % (32 * want) == 0) KS = want;

@@ -608,6 +608,7 @@ struct RowArgs {
     const double* norm2;  // ||row||^2
     long long n_rows;
     unsigned long long time0;  // rows consumed before this launch
+    const unsigned long long* times;  // explicit arrival time per row (TimeBasedSWFD), or NULL: time0 + r + 1
     int mode;
     int slot0;            // first slot handled by this launch
     long long batch;      // MODE_FD_BATCH
@@ -636,7 +637,7 @@ __global__ void __launch_bounds__(NT, 1) k_swfd_rows(Dev D, RowArgs A) {
     for (long long r = 0; r < A.n_rows; ++r) {
         const double* x = A.rows + (size_t)r * D.d;
         const double nx = A.norm2[r];
-        const unsigned long long t = A.time0 + (unsigned long long)r + 1ull;
+        const unsigned long long t = A.times ? A.times[r] : A.time0 + (unsigned long long)r + 1ull;
         // ---- A: scalar bookkeeping by the leader ------------------------------
         if (T.leader()) {
             sl.f_reset = 0;
@@ -654,8 +655,11 @@ __global__ void __launch_bounds__(NT, 1) k_swfd_rows(Dev D, RowArgs A) {
                 // fd_aux starts over with last_dump_time = time
                 const unsigned long long p = t / D.N;
                 if (p > sl.period) {
+                    // explicit times may skip whole periods: after two or more swaps both sides are
+                    // fresh (the `while self.period < self.time // self.N` loop, :66-75 / :99-107)
+                    const bool both = p >= sl.period + 2ull;
                     sl.period = p;
-                    if ((int)(p & 1ull) != sl.parity) {
+                    if (both || (int)(p & 1ull) != sl.parity) {
                         sl.f_reset = 1;
                         sl.n = D.ell; sl.b = 0; sl.q_ident = 1;
                         sl.energy = 0.0; sl.delta = 0.0;

@@ -472,6 +472,7 @@ struct Engine {
     unsigned char* raw = nullptr;  size_t raw_bytes = 0;
     double* stage = nullptr;
     double* norm2 = nullptr;
+    unsigned long long* times_dev = nullptr;   // explicit arrival times of the staged chunk
     // query scratch
     QueryScratch Q;
     double *o_sketch = nullptr, *o_vt = nullptr, *o_s2 = nullptr, *o_delta = nullptr;
@@ -593,6 +594,7 @@ static int engine_create(Engine** out, long long N, long long d, long long ell, 
     A_(E->raw, E->raw_bytes);
     A_(E->stage, (size_t)chunk_rows * d);
     A_(E->norm2, (size_t)chunk_rows);
+    A_(E->times_dev, (size_t)chunk_rows);
     QueryScratch& Q = E->Q;
     Q.ng_max = D.ell + D.capn + 1;
     Q.ng_max += Q.ng_max & 1;
@@ -664,13 +666,17 @@ static int stage_chunk(Engine& E, const void* dev_rows, long long n, long long l
 
 // feed rows chunk by chunk; `mode` selects the per-row rule set
 static int engine_feed(Engine& E, const void* rows, long long n_rows, long long ld, int dtype,
-                       int where, int mode, long long batch, cudaStream_t st) {
+                       int where, int mode, long long batch, cudaStream_t st,
+                       const unsigned long long* times_host = nullptr) {
     const size_t es = dtype_size(dtype);
     MUSED_REQUIRE(es != 0, "unknown dtype %d", dtype);
     MUSED_REQUIRE(n_rows >= 0 && ld >= E.D.d, "bad shape: n_rows=%lld ld=%lld d=%lld", n_rows, ld, E.D.d);
     MUSED_REQUIRE(rows != nullptr || n_rows == 0, "rows is NULL");
     MUSED_CUDA(cudaSetDevice(E.device));
-    if (E.D.S == 0) { E.time += (unsigned long long)n_rows; return 0; }
+    if (E.D.S == 0) {
+        E.time = (times_host && n_rows > 0) ? times_host[n_rows - 1] : E.time + (unsigned long long)n_rows;
+        return 0;
+    }
     long long done = 0;
     while (done < n_rows) {
         const long long n = std::min(E.chunk_rows, n_rows - done);
@@ -695,6 +701,11 @@ static int engine_feed(Engine& E, const void* rows, long long n_rows, long long 
         A.norm2 = E.norm2;
         A.n_rows = n;
         A.time0 = E.time;
+        if (times_host) {
+            MUSED_CUDA(cudaMemcpyAsync(E.times_dev, times_host + done, (size_t)n * sizeof(unsigned long long),
+                                       cudaMemcpyHostToDevice, st));
+            A.times = E.times_dev;
+        }
         A.mode = mode;
         A.slot0 = 0;
         A.batch = batch;
@@ -714,11 +725,11 @@ static int engine_feed(Engine& E, const void* rows, long long n_rows, long long 
             E.timed_launches += 1;
             E.timed_rows += n;
         }
-        E.time += (unsigned long long)n;
+        E.time = times_host ? times_host[done + n - 1] : E.time + (unsigned long long)n;
         done += n;
-        if (where == MUSED_HOST && done < n_rows) MUSED_CUDA(cudaStreamSynchronize(st));
+        if ((where == MUSED_HOST || times_host) && done < n_rows) MUSED_CUDA(cudaStreamSynchronize(st));
     }
-    if (where == MUSED_HOST) MUSED_CUDA(cudaStreamSynchronize(st));
+    if (where == MUSED_HOST || times_host) MUSED_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
 
@@ -827,6 +838,13 @@ int mused_swfd_fit(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld
     MUSED_REQUIRE(h, "NULL handle");
     if (h->B) return bengine_fit(h->B, rows, n_rows, ld, dtype, where, (cudaStream_t)stream);
     return engine_feed(*h->E, rows, n_rows, ld, dtype, where, MODE_SEQ, 0, (cudaStream_t)stream);
+}
+int mused_swfd_fit_timed(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld, int dtype,
+                         int where, const uint64_t* times, void* stream) {
+    MUSED_REQUIRE(h && (times || n_rows == 0), "NULL argument");
+    MUSED_REQUIRE(!h->B, "explicit arrival times (TimeBasedSWFD) are served by schedule=reference");
+    return engine_feed(*h->E, rows, n_rows, ld, dtype, where, MODE_SEQ, 0, (cudaStream_t)stream,
+                       reinterpret_cast<const unsigned long long*>(times));
 }
 int mused_swfd_time(mused_swfd_t* h, uint64_t* t) {
     MUSED_REQUIRE(h && t, "NULL argument");

@@ -162,3 +162,46 @@ class SeqBasedSWFD:
             self.close()
         except Exception:
             pass
+
+
+class TimeBasedSWFD(SeqBasedSWFD):
+    """TimeBasedSWFD on the B200 engine (swfd/seq_based_swfd.py:106-207): rows carry an explicit
+    arrival time, the ladder has ceil(log2(N R / sketch_dim)) levels with dump thresholds 2^j
+    (kwargs ``upper_F_norm`` / ``lower_F_norm`` as in :131-141), beta defaults to 4."""
+
+    def __init__(self, N: int, R: float, d: int, sketch_dim: int, beta: float = 4.0, *,
+                 device: int = 0, cluster: int = 0, chunk_rows: int = 0, **kwargs):
+        self.N = np.uint64(N)
+        self.d = int(d)
+        self.R = R
+        self.beta = beta
+        self.sketch_dim = int(sketch_dim)
+        self.log_eNR = int(np.ceil(np.log2(N * R / sketch_dim)))                       # :120
+        base = 1.0
+        if "upper_F_norm" in kwargs:                                                   # :131-141
+            self.log_eNR = int(np.ceil(np.log2(kwargs["upper_F_norm"] / self.sketch_dim)))
+            if "lower_F_norm" in kwargs:
+                self.log_eNR = int(np.ceil(np.log2(kwargs["upper_F_norm"] / kwargs["lower_F_norm"])))
+                base = kwargs["lower_F_norm"] / self.sketch_dim
+        thr = [float(base * (2 ** j)) for j in range(self.log_eNR)]                    # :139-146
+        self.logR = self.log_eNR
+        self.thresholds = thr
+        self.schedule = "reference"
+        lib = _lib.load()
+        arr = (C.c_double * max(1, len(thr)))(*thr)
+        cfg = _lib.SwfdCfg(int(N), self.d, self.sketch_dim, float(beta), len(thr), arr,
+                           int(device), int(cluster), int(chunk_rows), _lib.SCHEDULES["reference"], 0)
+        self._h = C.c_void_p()
+        _lib.check(lib.mused_swfd_create(C.byref(self._h), C.byref(cfg)))
+        self._lib = lib
+
+    def fit(self, X, t):
+        """Row(s) X arriving at time(s) t (:150-189): t is one integer for a (1, d) row, or a
+        non-decreasing sequence of n integers for (n, d) rows (= n single calls)."""
+        keep, ptr, n, ld, dt, where = _lib.rows_arg(X, self.d)
+        times = np.ascontiguousarray(np.broadcast_to(np.asarray(t, dtype=np.uint64).reshape(-1), (n,))
+                                     if np.ndim(t) == 0 else np.asarray(t, dtype=np.uint64).reshape(-1))
+        if times.shape[0] != n:
+            raise ValueError("%d arrival times for %d rows" % (times.shape[0], n))
+        _lib.check(self._lib.mused_swfd_fit_timed(self._h, ptr, n, ld, dt, where, times.ctypes.data, None))
+        del keep
