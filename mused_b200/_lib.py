@@ -108,6 +108,19 @@ def check(rc):
         raise RuntimeError("mused_b200: %s (code %d)" % (msg, rc))
 
 
+def current_stream(device=0):
+    """cudaStream_t (as int) of torch's current stream on ``device``; None (= the default stream)
+    when torch or CUDA is not there.  Independent sketches driven from different torch streams
+    overlap on the GPU (their kernels leave most SMs idle: one warp per SM sub-partition)."""
+    try:
+        import torch
+        if torch.cuda.is_available():
+            return int(torch.cuda.current_stream(device).cuda_stream) or None
+    except Exception:  # pragma: no cover
+        pass
+    return None
+
+
 def rows_arg(X, d):
     """(pointer, n_rows, ld, dtype, where) for a 2-D numpy array or torch tensor."""
     try:

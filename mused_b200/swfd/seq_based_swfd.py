@@ -57,6 +57,7 @@ class SeqBasedSWFD:
         self._h = C.c_void_p()
         _lib.check(lib.mused_swfd_create(C.byref(self._h), C.byref(cfg)))
         self._lib = lib
+        self._device = int(device)
 
     # -- reference API -----------------------------------------------------
     def fit(self, X):
@@ -67,7 +68,8 @@ class SeqBasedSWFD:
         CUDA) float64 / float32 / int64 / int32 / uint8 rows; copied.
         """
         keep, ptr, n, ld, dt, where = _lib.rows_arg(X, self.d)
-        _lib.check(self._lib.mused_swfd_fit(self._h, ptr, n, ld, dt, where, None))
+        _lib.check(self._lib.mused_swfd_fit(self._h, ptr, n, ld, dt, where,
+                                            _lib.current_stream(getattr(self, "_device", 0))))
         del keep
 
     def get(self):
@@ -82,7 +84,7 @@ class SeqBasedSWFD:
             raise KeyError(0)                                      # what the reference does
         _lib.check(self._lib.mused_swfd_get(self._h, sketch.ctypes.data, s2.ctypes.data,
                                             vt.ctypes.data, C.byref(delta), C.byref(level),
-                                            _lib.HOST, None))
+                                            _lib.HOST, _lib.current_stream(getattr(self, "_device", 0))))
         self.last_level = int(level.value)
         return sketch, s2, vt, float(delta.value)
 
@@ -194,6 +196,7 @@ class TimeBasedSWFD(SeqBasedSWFD):
         self._h = C.c_void_p()
         _lib.check(lib.mused_swfd_create(C.byref(self._h), C.byref(cfg)))
         self._lib = lib
+        self._device = int(device)
 
     def fit(self, X, t):
         """Row(s) X arriving at time(s) t (:150-189): t is one integer for a (1, d) row, or a
@@ -203,5 +206,6 @@ class TimeBasedSWFD(SeqBasedSWFD):
                                      if np.ndim(t) == 0 else np.asarray(t, dtype=np.uint64).reshape(-1))
         if times.shape[0] != n:
             raise ValueError("%d arrival times for %d rows" % (times.shape[0], n))
-        _lib.check(self._lib.mused_swfd_fit_timed(self._h, ptr, n, ld, dt, where, times.ctypes.data, None))
+        _lib.check(self._lib.mused_swfd_fit_timed(self._h, ptr, n, ld, dt, where, times.ctypes.data,
+                                                  _lib.current_stream(getattr(self, "_device", 0))))
         del keep

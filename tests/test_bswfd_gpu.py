@@ -139,3 +139,33 @@ def test_batched_engine_rejects_unsupported_shapes():
         SeqBasedSWFD(100, 8.0, 100, 16, schedule="batched")     # d % 32 != 0
     with pytest.raises(ValueError):
         SeqBasedSWFD(100, 8.0, 128, 16, schedule="nope")
+
+
+def test_independent_sketches_on_their_own_streams_match_sequential_runs():
+    """Several sketches driven from different CUDA streams overlap on the GPU (bench multi_stream
+    leg); interleaving their calls must not change any of them."""
+    import torch
+    from mused_b200.swfd import SeqBasedSWFD
+    ell, d, N, n = 32, 256, 600, 1500
+    data = [synth.lowrank_stream(n, d, seed=20 + k, scale=2.0) for k in range(3)]
+    R = max(synth.row_norm2_max(a) for a in data)
+    ref = []
+    for a in data:
+        sk = SeqBasedSWFD(N, R, d, ell, schedule="batched")
+        sk.fit(torch.as_tensor(a).cuda())
+        ref.append(sk.get())
+        sk.close()
+    sks = [SeqBasedSWFD(N, R, d, ell, schedule="batched") for _ in data]
+    streams = [torch.cuda.Stream() for _ in data]
+    dev = [torch.as_tensor(a).cuda() for a in data]
+    torch.cuda.synchronize()
+    for lo in range(0, n, 170):
+        for k, sk in enumerate(sks):
+            with torch.cuda.stream(streams[k]):
+                sk.fit(dev[k][lo:lo + 170])
+    for k, sk in enumerate(sks):
+        with torch.cuda.stream(streams[k]):
+            out = sk.get()
+        np.testing.assert_array_equal(out[1], ref[k][1])
+        np.testing.assert_array_equal(out[0], ref[k][0])
+        sk.close()
