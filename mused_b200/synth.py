@@ -84,3 +84,31 @@ def event_stream(n, blocks=(256, 192, 32, 32), n_events=150, noise_rate=0.95,
             off += b
         pos += r
     return X, labels, np.concatenate(centres, axis=1)
+
+
+def multimodal_event_stream(n, n_events=150, noise_rate=0.95, vis_dim=512, txt_dim=768, burst=400, seed=0):
+    """MediaEval-SED-shaped synthetic items (BASELINE configs[2]): per item a (latitude, longitude)
+    pair, (datetaken, dateupload) epoch seconds, a visual and a text embedding; events own a place,
+    a time and a centre per embedding, noise items (label 0, main.py:306) are spread uniformly.
+    Returns ([location, time, visual, text], modality_types, labels)."""
+    rng = np.random.default_rng([seed, 31])
+    ev_loc = np.column_stack([rng.uniform(-50, 50, n_events), rng.uniform(-150, 150, n_events)])
+    ev_time = 1.30e9 + rng.uniform(0, 3e7, n_events)
+    ev_vis = rng.standard_normal((n_events, vis_dim)).astype(np.float32)
+    ev_txt = rng.standard_normal((n_events, txt_dim)).astype(np.float32)
+    labels = np.zeros(n, dtype=np.int64)
+    is_noise = rng.random(n) < noise_rate
+    active = (np.arange(n) // burst) % n_events
+    other = rng.integers(0, n_events, n)
+    ev = np.where(rng.random(n) < 0.8, active, other)
+    labels[~is_noise] = ev[~is_noise] + 1
+    loc = np.column_stack([rng.uniform(-60, 60, n), rng.uniform(-180, 180, n)])
+    loc[~is_noise] = ev_loc[ev[~is_noise]] + rng.normal(0, 0.05, (int((~is_noise).sum()), 2))
+    t0 = 1.30e9 + rng.uniform(0, 3e7, n)
+    t0[~is_noise] = ev_time[ev[~is_noise]] + rng.normal(0, 3600, int((~is_noise).sum()))
+    tim = np.column_stack([t0, t0 + np.abs(rng.normal(0, 86400, n))])
+    vis = rng.standard_normal((n, vis_dim)).astype(np.float32)
+    vis[~is_noise] = ev_vis[ev[~is_noise]] + 0.3 * vis[~is_noise]
+    txt = rng.standard_normal((n, txt_dim)).astype(np.float32)
+    txt[~is_noise] = ev_txt[ev[~is_noise]] + 0.3 * txt[~is_noise]
+    return [loc, tim, vis.astype(np.float64), txt.astype(np.float64)], ["location", "time", "visual", "cosine"], labels
