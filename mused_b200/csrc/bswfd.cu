@@ -24,7 +24,7 @@ namespace mused {
 // reduction order for ||x||^2 (it decides routing, seq_based_swfd.py:76-77).
 // ---------------------------------------------------------------------------
 template <class Tin>
-__global__ void __launch_bounds__(256) k_bstage(const Tin* __restrict__ in, long long ld, long long d,
+__global__ void __launch_bounds__(256) k_bstage(const Tin* __restrict__ in, long long ld, long long d_in, long long d,
                                                 int row_off, float* __restrict__ xhi,
                                                 float* __restrict__ xlo, double* __restrict__ norm2) {
     __shared__ double red[8];
@@ -33,7 +33,7 @@ __global__ void __launch_bounds__(256) k_bstage(const Tin* __restrict__ in, long
     float* hi = xhi + (size_t)(row_off + r) * d;
     float* lo = xlo + (size_t)(row_off + r) * d;
     double acc = 0.0;
-    for (long long c = threadIdx.x; c < d; c += 256) {
+    for (long long c = threadIdx.x; c < d_in; c += 256) {    // columns d_in .. d-1 of the planes stay zero
         const float v = (float)src[c];
         float h, l;
         umma::split_tf32(v, h, l);
@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(256) k_bstage(const Tin* __restrict__ in, long
 // (the append is pure streaming: 4 bytes read and 8 written per element).  Same contract as
 // k_bstage: hi / lo planes and ||x||^2 in a fixed order (lane partials in element order, then the
 // xor tree) that does not depend on how the caller slices the stream.
-__global__ void __launch_bounds__(256) k_bstage_v4(const float* __restrict__ in, long long ld, long long d, long long m,
+__global__ void __launch_bounds__(256) k_bstage_v4(const float* __restrict__ in, long long ld, long long d_in, long long d, long long m,
                                                    int row_off, float* __restrict__ xhi, float* __restrict__ xlo,
                                                    double* __restrict__ norm2) {
     const int lane = threadIdx.x & 31;
@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(256) k_bstage_v4(const float* __restrict__ in,
         float4* hi = reinterpret_cast<float4*>(xhi + (size_t)(row_off + r) * d);
         float4* lo = reinterpret_cast<float4*>(xlo + (size_t)(row_off + r) * d);
         double acc = 0.0;
-        for (long long c = lane; c < d / 4; c += 32) {
+        for (long long c = lane; c < d_in / 4; c += 32) {
             const float4 v = __ldcs(src + c);
             float4 h, l;
             umma::split_tf32(v.x, h.x, l.x);
@@ -155,12 +155,13 @@ __global__ void __launch_bounds__(256) k_bbook(BDev D, int n, unsigned long long
         }
         for (int i = threadIdx.x; i < D.ell; i += 256) D.s2[(size_t)s * D.ell + i] = 0.0;
     }
-    for (int k = 0; k < nr; ++k) {
-        const float* h = D.xhi + (size_t)(D.x0 + raw_row[k]) * D.d;
-        const float* l = D.xlo + (size_t)(D.x0 + raw_row[k]) * D.d;
-        float* dst = D.ringV + ((size_t)s * D.capn + raw_slot[k]) * D.d;
-        for (long long c = threadIdx.x; c < D.d; c += 256) dst[c] = h[c] + l[c];
+    // the rows themselves are copied into the ring by K4's CTAs (one column tile each), not by this one CTA
+    int* rl = D.raw_list + (size_t)s * 2 * D.ell;
+    for (int k = threadIdx.x; k < nr; k += 256) {
+        rl[k] = raw_row[k];
+        rl[D.ell + k] = raw_slot[k];
     }
+    if (threadIdx.x == 0) sl.nraw = nr;
 }
 
 // split-K reduction of K2's partial Grams, float64, fixed order (deterministic)
@@ -292,13 +293,18 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
         return MUSED_ERR_CUDA;
     }
     MUSED_REQUIRE(device >= 0 && device < ndev, "device %d out of range (have %d)", device, ndev);
-    MUSED_REQUIRE(ell == 16 || ell == 32 || ell == 64 || ell == 128,
-                  "schedule=batched supports sketch_dim 16, 32, 64 or 128 (got %lld); use schedule=reference", ell);
-    MUSED_REQUIRE(d % 32 == 0 && d > ell, "schedule=batched needs d %% 32 == 0 and d > sketch_dim (d=%lld)", d);
+    MUSED_REQUIRE(ell >= 2 && ell <= BS_MAX_ELL,
+                  "schedule=batched supports sketch_dim 2 .. %d (got %lld); use schedule=reference", BS_MAX_ELL, ell);
+    MUSED_REQUIRE(d > ell, "schedule=batched needs d > sketch_dim (d=%lld, sketch_dim=%lld)", d, ell);
+    // The kernels run on sketch_dim in {16, 32, 64, 128} and d %% 32 == 0; any other shape is embedded in the
+    // next such one with zero rows / columns, which changes no Gram entry, eigenvalue or product.
+    const long long ell_l = ell, d_l = d;
+    ell = ell_l <= 16 ? 16 : (ell_l <= 32 ? 32 : (ell_l <= 64 ? 64 : 128));
+    d = (d_l + 31) / 32 * 32;
     MUSED_REQUIRE(N >= 1 && beta > 0, "bad N / beta");
     MUSED_REQUIRE(n_levels >= 0 && n_levels <= 64, "n_levels out of range");
-    if (batch <= 0) batch = ell;
-    MUSED_REQUIRE(batch <= ell, "batch_rows must be <= sketch_dim");
+    if (batch <= 0) batch = ell_l;
+    MUSED_REQUIRE(batch <= ell_l, "batch_rows must be <= sketch_dim");
     MUSED_CUDA(cudaSetDevice(device));
     BEngine* E = new BEngine();
     E->device = device;
@@ -311,10 +317,12 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     const int S = 2 * n_levels;
     D.S = S;
     D.ell = (int)ell;
+    D.ell_l = (int)ell_l;
     D.n2 = 2 * (int)ell;
     D.d = d;
+    D.d_l = d_l;
     D.N = (unsigned long long)N;
-    D.qcap = (2.0 + 8.0 / beta) * (double)ell;
+    D.qcap = (2.0 + 8.0 / beta) * (double)ell_l;   // seq_based_swfd.py:61
     D.capn = (int)floor(D.qcap) + (int)batch + (int)ell + 2;
     // split-K: enough CTAs to cover the SMs, K slices of whole 32-float blocks
     int KS = 16;
@@ -342,6 +350,7 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     A_(D.Tlo, Sa * ell * D.n2 + 128 * D.n2);
     A_(D.s2, Sa * ell);
     A_(D.dump_slot, Sa * ell);
+    A_(D.raw_list, Sa * 2 * ell);
     A_(D.ringV, Sa * D.capn * d);
     A_(D.ringS, Sa * D.capn);
     A_(D.ringT, Sa * D.capn);
@@ -446,6 +455,7 @@ static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t 
     A.slots = E.D.slots;
     A.G = E.D.G;
     A.ell = E.D.ell;
+    A.ell_l = E.D.ell_l;
     A.n2 = E.D.n2;
     A.capn = E.D.capn;
     A.mask = E.D.mask;
@@ -567,17 +577,17 @@ static int stage_rows(BEngine& E, const void* dev_rows, long long m, long long l
     MUSED_REQUIRE(row_off + m <= E.sb_rows + D.ell, "internal: staging planes overflow (%d + %lld rows)", row_off, m);
     E.mark(0, st);
     switch (dtype) {
-        case MUSED_F64: k_bstage<double><<<(unsigned)m, 256, 0, st>>>((const double*)dev_rows, ld, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_F64: k_bstage<double><<<(unsigned)m, 256, 0, st>>>((const double*)dev_rows, ld, D.d_l, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
         case MUSED_F32:
-            if (D.d % 4 == 0 && ld % 4 == 0 && ((uintptr_t)dev_rows & 15) == 0)
+            if (D.d_l % 4 == 0 && ld % 4 == 0 && ((uintptr_t)dev_rows & 15) == 0)
                 k_bstage_v4<<<(unsigned)std::min<long long>((m + 7) / 8, 16ll * E.sm_count), 256, 0, st>>>(
-                    (const float*)dev_rows, ld, D.d, m, row_off, D.xhi, D.xlo, D.norm2);
+                    (const float*)dev_rows, ld, D.d_l, D.d, m, row_off, D.xhi, D.xlo, D.norm2);
             else
-                k_bstage<float><<<(unsigned)m, 256, 0, st>>>((const float*)dev_rows, ld, D.d, row_off, D.xhi, D.xlo, D.norm2);
+                k_bstage<float><<<(unsigned)m, 256, 0, st>>>((const float*)dev_rows, ld, D.d_l, D.d, row_off, D.xhi, D.xlo, D.norm2);
             break;
-        case MUSED_I64: k_bstage<long long><<<(unsigned)m, 256, 0, st>>>((const long long*)dev_rows, ld, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
-        case MUSED_I32: k_bstage<int><<<(unsigned)m, 256, 0, st>>>((const int*)dev_rows, ld, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
-        case MUSED_U8: k_bstage<unsigned char><<<(unsigned)m, 256, 0, st>>>((const unsigned char*)dev_rows, ld, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_I64: k_bstage<long long><<<(unsigned)m, 256, 0, st>>>((const long long*)dev_rows, ld, D.d_l, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_I32: k_bstage<int><<<(unsigned)m, 256, 0, st>>>((const int*)dev_rows, ld, D.d_l, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_U8: k_bstage<unsigned char><<<(unsigned)m, 256, 0, st>>>((const unsigned char*)dev_rows, ld, D.d_l, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
     }
     MUSED_CUDA(cudaGetLastError());
     E.mark(0, st);
@@ -608,10 +618,10 @@ int bengine_fit(BEngine* Ep, const void* rows, long long n_rows, long long ld, i
     BEngine& E = *Ep;
     const size_t es = b_dtype_size(dtype);
     MUSED_REQUIRE(es != 0, "unknown dtype %d", dtype);
-    MUSED_REQUIRE(n_rows >= 0 && ld >= E.D.d, "bad shape: n_rows=%lld ld=%lld d=%lld", n_rows, ld, E.D.d);
+    MUSED_REQUIRE(n_rows >= 0 && ld >= E.D.d_l, "bad shape: n_rows=%lld ld=%lld d=%lld", n_rows, ld, E.D.d_l);
     MUSED_REQUIRE(rows != nullptr || n_rows == 0, "rows is NULL");
     MUSED_CUDA(cudaSetDevice(E.device));
-    const long long d = E.D.d;
+    const long long d = E.D.d_l;
     const long long host_rows = (long long)(E.raw_bytes / ((size_t)d * es));
     long long fed = 0;
     while (fed < n_rows) {
@@ -631,7 +641,7 @@ int bengine_fit(BEngine* Ep, const void* rows, long long n_rows, long long ld, i
         while (off < blk) {
             // stage as many of the block's rows as the planes take, in one launch ...
             long long space = E.sb_rows - (E.D.x0 + E.pend);
-            if (space < std::min<long long>(blk - off, E.D.ell)) {
+            if (space < std::min<long long>(blk - off, E.batch)) {
                 int rc = compact_open_chunk(E, st);
                 if (rc) return rc;
                 space = E.sb_rows - E.pend;
@@ -679,7 +689,7 @@ int bengine_size(BEngine* E, long long* n) {
     int rc = b_read_slots(*E, sl);
     if (rc) return rc;
     long long tot = 0;
-    for (int j = 0; j < E->n_levels; ++j) tot += sl[2 * j].q_len + sl[2 * j + 1].q_len + 2ll * E->D.ell;
+    for (int j = 0; j < E->n_levels; ++j) tot += sl[2 * j].q_len + sl[2 * j + 1].q_len + 2ll * E->D.ell_l;
     *n = tot;
     return 0;
 }
@@ -688,6 +698,14 @@ static int b_copy_out(double* dst, const double* src, size_t n, int where, cudaS
     if (!dst) return 0;
     MUSED_CUDA(cudaMemcpyAsync(dst, src, n * sizeof(double),
                                where == MUSED_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
+// rows x cols (the caller's sketch_dim x d, packed) out of a matrix with the physical row length ld
+static int b_copy_out_2d(double* dst, const double* src, size_t rows, size_t cols, size_t ld, int where, cudaStream_t st) {
+    if (!dst) return 0;
+    if (cols == ld) return b_copy_out(dst, src, rows * cols, where, st);
+    MUSED_CUDA(cudaMemcpy2DAsync(dst, cols * sizeof(double), src, ld * sizeof(double), cols * sizeof(double), rows,
+                                 where == MUSED_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
     return 0;
 }
 
@@ -744,21 +762,20 @@ int bengine_get_finish(BEngine* Ep, double* sketch, double* sigma2, double* vt, 
     BDev& D = E.D;
     int rc = 0;
     const int s = E.q_slot;
-    const size_t ld_out = (size_t)D.ell * D.d;
     if (E.q_ng == 0) {
         k_bfd_out<<<E.sm_count, 256, 0, st>>>(D, s, E.o_sketch, E.o_s2, vt ? E.o_vt : nullptr, E.o_delta);
         MUSED_CUDA(cudaGetLastError());
         mused_count_launches(1);
     } else {
         // single-GPU get(): Gram or covariance side, whichever is smaller; phase API: the Gram is in Q.G
-        if (E.q_gram) rc = merge_query_solve(E.Q, E.q_ng, D.d, D.ell, E.sm_count, E.o_sketch, vt ? E.o_vt : nullptr, E.o_s2, st);
-        else rc = merge_query(E.Q, E.q_ng, D.d, D.ell, E.sm_count, E.o_sketch, vt ? E.o_vt : nullptr, E.o_s2, st);
+        if (E.q_gram) rc = merge_query_solve(E.Q, E.q_ng, D.d, D.ell_l, E.sm_count, E.o_sketch, vt ? E.o_vt : nullptr, E.o_s2, st);
+        else rc = merge_query(E.Q, E.q_ng, D.d, D.ell_l, E.sm_count, E.o_sketch, vt ? E.o_vt : nullptr, E.o_s2, st);
         if (rc) return rc;
         MUSED_CUDA(cudaMemsetAsync(E.o_delta, 0, sizeof(double), st));
     }
-    if ((rc = b_copy_out(sketch, E.o_sketch, ld_out, where, st))) return rc;
-    if ((rc = b_copy_out(sigma2, E.o_s2, (size_t)D.ell, where, st))) return rc;
-    if ((rc = b_copy_out(vt, E.o_vt, ld_out, where, st))) return rc;
+    if ((rc = b_copy_out_2d(sketch, E.o_sketch, (size_t)D.ell_l, (size_t)D.d_l, (size_t)D.d, where, st))) return rc;
+    if ((rc = b_copy_out(sigma2, E.o_s2, (size_t)D.ell_l, where, st))) return rc;
+    if ((rc = b_copy_out_2d(vt, E.o_vt, (size_t)D.ell_l, (size_t)D.d_l, (size_t)D.d, where, st))) return rc;
     if (delta) MUSED_CUDA(cudaMemcpyAsync(delta, E.o_delta, sizeof(double), cudaMemcpyDeviceToHost, st));
     MUSED_CUDA(cudaStreamSynchronize(st));
     return 0;
@@ -798,16 +815,16 @@ int bengine_stage(BEngine* Ep, const void* rows, long long m, long long ld, int 
     const size_t es = b_dtype_size(dtype);
     MUSED_REQUIRE(es != 0, "unknown dtype %d", dtype);
     MUSED_REQUIRE(m >= 0 && m <= chunk_room(E), "stage: %lld rows do not fit the open chunk (room %lld)", m, chunk_room(E));
-    MUSED_REQUIRE(ld >= E.D.d && (rows || m == 0), "bad rows / ld");
+    MUSED_REQUIRE(ld >= E.D.d_l && (rows || m == 0), "bad rows / ld");
     if (m == 0) return 0;
     MUSED_CUDA(cudaSetDevice(E.device));
     const void* dev = rows;
     long long dev_ld = ld;
     if (where == MUSED_HOST) {
-        MUSED_REQUIRE((size_t)m * E.D.d * es <= E.raw_bytes, "stage: block too large");
-        MUSED_CUDA(cudaMemcpy2DAsync(E.raw, (size_t)E.D.d * es, rows, (size_t)ld * es, (size_t)E.D.d * es, (size_t)m, cudaMemcpyHostToDevice, st));
+        MUSED_REQUIRE((size_t)m * E.D.d_l * es <= E.raw_bytes, "stage: block too large");
+        MUSED_CUDA(cudaMemcpy2DAsync(E.raw, (size_t)E.D.d_l * es, rows, (size_t)ld * es, (size_t)E.D.d_l * es, (size_t)m, cudaMemcpyHostToDevice, st));
         dev = E.raw;
-        dev_ld = E.D.d;
+        dev_ld = E.D.d_l;
     }
     int rc = stage_rows(E, dev, m, dev_ld, dtype, true, st);
     if (rc) return rc;
@@ -822,7 +839,7 @@ int bengine_debug(BEngine* Ep, double* scal, double* sigma2, unsigned long long*
     std::vector<BSlot> sl;
     int rc = b_read_slots(E, sl);
     if (rc) return rc;
-    const int capn = E.D.capn, ell = E.D.ell;
+    const int capn = E.D.capn, ell = E.D.ell_l, ell_p = E.D.ell;
     std::vector<unsigned long long> rs(capn), rt(capn);
     for (int j = 0; j < E.n_levels; ++j) {
         for (int side = 0; side < 2; ++side) {
@@ -836,7 +853,7 @@ int bengine_debug(BEngine* Ep, double* scal, double* sigma2, unsigned long long*
                 r[5] = (double)sl[s].n_flush; r[6] = (double)sl[s].n_dump; r[7] = (double)sl[s].n_raw;
             }
             if (sigma2)
-                MUSED_CUDA(cudaMemcpy(sigma2 + (size_t)o * ell, E.D.s2 + (size_t)s * ell, sizeof(double) * ell, cudaMemcpyDeviceToHost));
+                MUSED_CUDA(cudaMemcpy(sigma2 + (size_t)o * ell, E.D.s2 + (size_t)s * ell_p, sizeof(double) * ell, cudaMemcpyDeviceToHost));
             if (q_s || q_t) {
                 MUSED_REQUIRE(q_cap >= sl[s].q_len, "q_cap too small");
                 MUSED_CUDA(cudaMemcpy(rs.data(), E.D.ringS + (size_t)s * capn, 8 * (size_t)capn, cudaMemcpyDeviceToHost));

@@ -9,9 +9,11 @@ namespace mused {
 constexpr int BS_MAX_ELL = 128;
 
 struct BDev {
-    int S, ell, n2, capn, KS;
+    int S, ell, n2, capn, KS;  // ell = PHYSICAL sketch rows (16 / 32 / 64 / 128), n2 = 2 ell
+    int ell_l;                 // the caller's sketch_dim <= ell; rows ell_l .. ell-1 of every sketch stay zero
     int x0;                    // row of the staging planes where the open chunk starts
-    long long d;
+    long long d;               // PHYSICAL row length (multiple of 32); columns d_l .. d-1 stay zero
+    long long d_l;             // the caller's d
     unsigned long long N;
     double qcap;
     BSlot* slots;
@@ -24,6 +26,7 @@ struct BDev {
     float *Thi, *Tlo;          // [S][ell][n2] rotate coefficients (TF32 hi / lo planes)
     double* s2;                // [S][ell]
     int* dump_slot;            // [S][ell]
+    int* raw_list;             // [S][2][ell] chunk rows that became raw snapshots | their ring entries (K5 -> K4)
     float* ringV;              // [S][capn][d] snapshot rows
     unsigned long long *ringS, *ringT;
 };

@@ -35,13 +35,14 @@ struct BSlot {                               // one FD instance of the batched e
     int q_head, q_len;
     int cur, src;                            // ping-pong plane holding the sketch / source of the pending rotate
     int parity, skip, npend, nd;
-    int sweeps, pad;
+    int sweeps, nraw;                        // nraw: raw-row snapshots of the current chunk (K5 -> K4 copies the rows)
 };
 
 struct EigArgs {
     BSlot* slots;
     const double* G;         // [S][n2][n2] Gram (split-K partials already added, all column shards)
     int ell, n2, capn;
+    int ell_l;               // logical sketch_dim (<= ell): shrink at rank ell_l, ranks >= ell_l give zero rows
     const unsigned char* mask;  // [S][ell] 1 = row of the chunk is NOT part of this instance's batch
     int n_rows;              // rows in the chunk
     unsigned long long t_end;
@@ -507,7 +508,7 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
         const uint32_t dst = dsmem_addr(&sm.cut, lane);
 #pragma unroll
         for (int k = 0; k < 8; ++k)
-            if (rk[k] == ELL) dsmem_st(dst, lamv[k]);
+            if (rk[k] == A.ell_l) dsmem_st(dst, lamv[k]);
     }
     cluster_barrier();
     const double cut = sm.cut;
@@ -521,7 +522,7 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
         const int r = rk[k];
         if (r >= ELL) continue;
         const double lam = lamv[k];
-        const double s2v = fmax(lam - cut, 0.0);
+        const double s2v = (r < A.ell_l) ? fmax(lam - cut, 0.0) : 0.0;
         const double coef = (lam > 0.0 && s2v > 0.0) ? sqrt(s2v / lam) / lam : 0.0;
 #pragma unroll
         for (int e = 0; e < EPL; ++e) {

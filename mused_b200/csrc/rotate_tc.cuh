@@ -38,7 +38,25 @@ k_rotate_tc(const __grid_constant__ CUtensorMap tm_t_hi, const __grid_constant__
     using C = RotCfg;
     const int s = blockIdx.y;
     const BSlot& sl = D.slots[s];
-    if (sl.skip) return;
+    // raw-row snapshots of this chunk (sliding_windows_frequent_directions.py:56-80): this CTA's 128 columns
+    // of every such row, staging planes -> ring entry chosen by K5.  `nw` warps, warp `wi` takes rows wi, wi+nw, ..
+    const int nraw = sl.nraw;
+    auto raw_copy = [&](int wi, int nw) {
+        const int* rl = D.raw_list + (size_t)s * 2 * D.ell;
+        const long long c = (long long)blockIdx.x * RotCfg::NT + 4 * (threadIdx.x & 31);
+        if (c >= D.d) return;
+        for (int k = wi; k < nraw; k += nw) {
+            const size_t xr = (size_t)(D.x0 + rl[k]) * D.d + c;
+            const float4 h = *reinterpret_cast<const float4*>(D.xhi + xr);
+            const float4 l = *reinterpret_cast<const float4*>(D.xlo + xr);
+            *reinterpret_cast<float4*>(D.ringV + ((size_t)s * D.capn + rl[D.ell + k]) * D.d + c) =
+                make_float4(h.x + l.x, h.y + l.y, h.z + l.z, h.w + l.w);
+        }
+    };
+    if (sl.skip) {
+        if (nraw > 0) raw_copy(threadIdx.x >> 5, 6);
+        return;
+    }
     extern __shared__ unsigned char smem_dyn[];
     unsigned char* base = (unsigned char*)(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
     uint64_t* full = (uint64_t*)(base + C::NST * C::STAGE_BYTES);
@@ -131,6 +149,7 @@ k_rotate_tc(const __grid_constant__ CUtensorMap tm_t_hi, const __grid_constant__
         }
     } else {
         const int q = warp & 3;
+        if (nraw > 0) raw_copy(warp - 2, 4);             // under the TMA / MMA pipeline of warps 0 and 1
         umma::mbar_wait(accum, 0);
         umma::tc_fence_after();
         const int r = q * 32 + lane;

@@ -55,6 +55,10 @@ def _check_query(gpu, ora, Aw):
     (32, 256, 700, 2100, 2.0),
     (64, 512, 1000, 2500, 2.0),        # BASELINE configs[0] shape (d=512, l=64), shortened
     (128, 1024, 2000, 4000, 2.0),      # BASELINE configs[1] shape (d=1024, l=128), shortened
+    (50, 600, 600, 1800, 2.0),         # main.py's default reduced_dim=50 on W=d=600: padded to l=64, d=608 inside
+    (24, 100, 400, 1200, 1.0),         # neither l nor d a kernel shape
+    (100, 1000, 1500, 3200, 2.0),
+    (3, 40, 200, 700, 1.0),
 ])
 def test_batched_engine_matches_batched_oracle(ell, d, N, n, scale):
     from mused_b200.swfd import SeqBasedSWFD
@@ -134,9 +138,9 @@ def test_batched_engine_adjacency_rows_and_cov_error_vs_reference_schedule():
 def test_batched_engine_rejects_unsupported_shapes():
     from mused_b200.swfd import SeqBasedSWFD
     with pytest.raises(ValueError):
-        SeqBasedSWFD(100, 8.0, 128, 24, schedule="batched")     # sketch_dim not in {16,32,64,128}
+        SeqBasedSWFD(100, 8.0, 1024, 200, schedule="batched")   # sketch_dim > 128
     with pytest.raises(ValueError):
-        SeqBasedSWFD(100, 8.0, 100, 16, schedule="batched")     # d % 32 != 0
+        SeqBasedSWFD(100, 8.0, 16, 16, schedule="batched")      # d <= sketch_dim
     with pytest.raises(ValueError):
         SeqBasedSWFD(100, 8.0, 128, 16, schedule="nope")
 
