@@ -21,7 +21,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--expt-extended-lambda", "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC",
     "-diag-suppress", "70",
-]
+] + os.environ.get("MUSED_NVCC_EXTRA", "").split()      # e.g. -DMUSED_EIG_PROF (cycle accounting of K3)
 
 
 def _digest():

@@ -346,6 +346,7 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     A_(D.mask, Sa * ell);
     A_(D.Gp, Sa * KS * D.n2 * D.n2);
     A_(D.G, Sa * D.n2 * D.n2);
+    A_(D.Gs, Sa * D.n2 * D.n2);
     A_(D.Thi, Sa * ell * D.n2 + 128 * D.n2);   // + slack: the 128-row T box of the last instance
     A_(D.Tlo, Sa * ell * D.n2 + 128 * D.n2);
     A_(D.s2, Sa * ell);
@@ -444,9 +445,11 @@ template <int EPL>
 static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t st) {
     static bool attr_set = false;
     static bool p2p = false;
+    static int mixed = 0;
     const int smem = (int)sizeof(EigSmem<EPL>);
     if (!attr_set) {
         p2p = getenv("MUSED_EIG_P2P") && atoi(getenv("MUSED_EIG_P2P")) != 0;
+        mixed = getenv("MUSED_EIG_MIXED") ? atoi(getenv("MUSED_EIG_MIXED")) : 1;   // 0 = float64 sweeps only
         MUSED_CUDA(cudaFuncSetAttribute(k_eig_jacobi<EPL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         MUSED_CUDA(cudaFuncSetAttribute(k_eig_jacobi<EPL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_set = true;
@@ -469,6 +472,8 @@ static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t 
     A.ringT = E.D.ringT;
     A.tol = 1e-3;          // quadratic phase: the sweep that measures <= 1e-3 leaves ~1e-6 (Gram accuracy)
     A.max_sweeps = 24;
+    A.mixed = mixed;
+    A.Gs = E.D.Gs;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(E.D.S * EPL));
     cfg.blockDim = dim3(EIG_NT);

@@ -23,6 +23,7 @@ struct BDev {
     unsigned char* mask;       // [S][ell] 1 = chunk row is a raw snapshot at this instance's level
     float* Gp;                 // [S][KS][n2][n2] split-K partials of K2
     double* G;                 // [S][n2][n2] their float64 sum (the buffer a column-sharded run allreduces)
+    double* Gs;                // [S][n2][n2] K3 scratch: symmetrised, masked Gram (mixed-precision eigensolve)
     float *Thi, *Tlo;          // [S][ell][n2] rotate coefficients (TF32 hi / lo planes)
     double* s2;                // [S][ell]
     int* dump_slot;            // [S][ell]

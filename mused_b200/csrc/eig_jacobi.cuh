@@ -53,6 +53,8 @@ struct EigArgs {
     unsigned long long* ringT;
     double tol;              // convergence: max |x.y| / (|x||y|)
     int max_sweeps;
+    int mixed;               // 1 = float32 sweeps first, then W = G V32 and float64 sweeps (see k_eig_jacobi)
+    double* Gs;              // [S][n2][n2] scratch: the symmetrised, masked Gram (mixed only)
 };
 
 template <int EPL>
@@ -87,6 +89,10 @@ __device__ __forceinline__ double dsmem_ld(uint32_t addr) {
 }
 __device__ __forceinline__ void dsmem_st(uint32_t addr, double v) {
     asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
+__device__ __forceinline__ void dsmem_ld_t(uint32_t addr, double& v) { v = dsmem_ld(addr); }
+__device__ __forceinline__ void dsmem_ld_t(uint32_t addr, float& v) {
+    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
 }
 __device__ __forceinline__ void cluster_barrier() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -127,33 +133,48 @@ __device__ __forceinline__ double rcp_approx(double x) {         // MUFU.RCP64H:
     return y;
 }
 __device__ __forceinline__ double sel(bool p, double a, double b) { return p ? a : b; }
+__device__ __forceinline__ float sel(bool p, float a, float b) { return p ? a : b; }
+__device__ __forceinline__ float rsqrt_approx(float x) {         // MUFU.RSQ
+    float y;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {           // MUFU.RCP
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 
 // Hestenes rotation of a column pair with inner product g and squared norms
-// (nx, ny): branch-free, float64 pipe only (no fp32 detour: F2F conversions and
-// IEEE fp32 division cost more issue slots than they save).  The TANGENT comes
+// (nx, ny): branch-free.  float64: float64 pipe only (no fp32 detour: F2F conversions
+// and IEEE fp32 division cost more issue slots than they save).  The TANGENT comes
 // from 20-bit MUFU seeds (t = b sgn(a) / (|a| + sqrt(a^2 + b^2)), a = ny - nx,
 // b = 2g), which is all the convergence needs; (c, s) is then refined so that
 // c^2 + s^2 = 1 to 1e-16 (two Newton steps on rsqrt(1 + t^2)), i.e. W stays G
 // times an orthogonal matrix.  Norms follow the rotation actually applied.
-__device__ __forceinline__ void jacobi_angle(double g, double nx, double ny, double nmax, double& off,
-                                             double& c, double& s, double& mx, double& my) {
-    const double prod = nx * ny;
-    const double rel = fabs(g) * rsqrt_approx(prod);
-    const bool live = prod > 0.0;
-    if (live && prod > 1e-24 * nmax * nmax) off = fmax(off, rel);
-    const bool apply = live && rel > 1e-10;
-    const double a = ny - nx, b = g + g;
-    const double q2 = fma(a, a, b * b);
-    const double r = q2 * rsqrt_approx(q2);
-    const double tb = b * rcp_approx(fabs(a) + r);
-    const double t = sel(a < 0.0, -tb, tb);
-    const double u = fma(t, t, 1.0);
-    double c0 = rsqrt_approx(u);
-    c0 = c0 * fma(-0.5 * u, c0 * c0, 1.5);
-    c0 = c0 * fma(-0.5 * u, c0 * c0, 1.5);     // 20 -> 40 -> 80 bits
-    c = sel(apply, c0, 1.0);
-    s = sel(apply, c0 * t, 0.0);
-    const double cc = c * c, ss = s * s, cs2 = (c + c) * s * g;
+// float32 (the first phase of the mixed-precision solve): same formulas, no refinement.
+template <class T>
+__device__ __forceinline__ void jacobi_angle(T g, T nx, T ny, T nmax, T& off, T& c, T& s, T& mx, T& my) {
+    constexpr bool F64 = sizeof(T) == 8;
+    const T prod = nx * ny;
+    const T rel = fabs(g) * rsqrt_approx(prod);
+    const bool live = prod > T(0);
+    if (live && prod > (F64 ? T(1e-24) : T(1e-12)) * nmax * nmax) off = fmax(off, rel);
+    const bool apply = live && rel > (F64 ? T(1e-10) : T(3e-8));
+    const T a = ny - nx, b = g + g;
+    const T q2 = fma(a, a, b * b);
+    const T r = q2 * rsqrt_approx(q2);
+    const T tb = b * rcp_approx(fabs(a) + r);
+    const T t = sel(a < T(0), -tb, tb);
+    const T u = fma(t, t, T(1));
+    T c0 = rsqrt_approx(u);
+    if (F64) {
+        c0 = c0 * fma(T(-0.5) * u, c0 * c0, T(1.5));
+        c0 = c0 * fma(T(-0.5) * u, c0 * c0, T(1.5));     // 20 -> 40 -> 80 bits
+    }
+    c = sel(apply, c0, T(1));
+    s = sel(apply, c0 * t, T(0));
+    const T cc = c * c, ss = s * s, cs2 = (c + c) * s * g;
     mx = fma(cc, nx, fma(ss, ny, -cs2));     // |c x - s y|^2
     my = fma(ss, nx, fma(cc, ny, cs2));      // |s x + c y|^2
 }
@@ -162,15 +183,14 @@ __device__ __forceinline__ void jacobi_angle(double g, double nx, double ny, dou
 // The four inner products are reduced together (6 shuffles instead of 20: after
 // the xor-16 and xor-8 steps lane group q = lane/8 owns product q), group q
 // computes the angle of rotation q, and (c, s, new norms) are broadcast back.
-template <int EPL, int A0, int B0, int A1, int B1, int A2, int B2, int A3, int B3>
-__device__ __forceinline__ void rot4(double (&col)[8][EPL], double (&nrm)[8], double nmax, double& off,
-                                     int lane) {
+template <class T, int EPL, int A0, int B0, int A1, int B1, int A2, int B2, int A3, int B3>
+__device__ __forceinline__ void rot4(T (&col)[8][EPL], T (&nrm)[8], T nmax, T& off, int lane) {
     constexpr int IA[4] = {A0, A1, A2, A3};
     constexpr int IB[4] = {B0, B1, B2, B3};
-    double g[4];
+    T g[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        double g0 = 0.0, g1 = 0.0;
+        T g0 = T(0), g1 = T(0);
 #pragma unroll
         for (int e = 0; e < EPL; e += 2) {
             g0 = fma(col[IA[k]][e], col[IB[k]][e], g0);
@@ -179,26 +199,26 @@ __device__ __forceinline__ void rot4(double (&col)[8][EPL], double (&nrm)[8], do
         g[k] = g0 + g1;
     }
     const bool h16 = (lane & 16) != 0, h8 = (lane & 8) != 0;
-    double k0 = sel(h16, g[2], g[0]) + __shfl_xor_sync(0xffffffffu, sel(h16, g[0], g[2]), 16);
-    double k1 = sel(h16, g[3], g[1]) + __shfl_xor_sync(0xffffffffu, sel(h16, g[1], g[3]), 16);
-    double gq = sel(h8, k1, k0) + __shfl_xor_sync(0xffffffffu, sel(h8, k0, k1), 8);
+    T k0 = sel(h16, g[2], g[0]) + __shfl_xor_sync(0xffffffffu, sel(h16, g[0], g[2]), 16);
+    T k1 = sel(h16, g[3], g[1]) + __shfl_xor_sync(0xffffffffu, sel(h16, g[1], g[3]), 16);
+    T gq = sel(h8, k1, k0) + __shfl_xor_sync(0xffffffffu, sel(h8, k0, k1), 8);
     gq += __shfl_xor_sync(0xffffffffu, gq, 4);
     gq += __shfl_xor_sync(0xffffffffu, gq, 2);
     gq += __shfl_xor_sync(0xffffffffu, gq, 1);
     // lanes 0-7: rotation 0, 8-15: rotation 1, 16-23: rotation 2, 24-31: rotation 3
-    const double nx = sel(h16, sel(h8, nrm[IA[3]], nrm[IA[2]]), sel(h8, nrm[IA[1]], nrm[IA[0]]));
-    const double ny = sel(h16, sel(h8, nrm[IB[3]], nrm[IB[2]]), sel(h8, nrm[IB[1]], nrm[IB[0]]));
-    double cq, sq, mxq, myq;
+    const T nx = sel(h16, sel(h8, nrm[IA[3]], nrm[IA[2]]), sel(h8, nrm[IA[1]], nrm[IA[0]]));
+    const T ny = sel(h16, sel(h8, nrm[IB[3]], nrm[IB[2]]), sel(h8, nrm[IB[1]], nrm[IB[0]]));
+    T cq, sq, mxq, myq;
     jacobi_angle(gq, nx, ny, nmax, off, cq, sq, mxq, myq);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const double c = __shfl_sync(0xffffffffu, cq, 8 * k);
-        const double s = __shfl_sync(0xffffffffu, sq, 8 * k);
+        const T c = __shfl_sync(0xffffffffu, cq, 8 * k);
+        const T s = __shfl_sync(0xffffffffu, sq, 8 * k);
         nrm[IA[k]] = __shfl_sync(0xffffffffu, mxq, 8 * k);
         nrm[IB[k]] = __shfl_sync(0xffffffffu, myq, 8 * k);
 #pragma unroll
         for (int e = 0; e < EPL; ++e) {
-            const double xv = col[IA[k]][e], yv = col[IB[k]][e];
+            const T xv = col[IA[k]][e], yv = col[IB[k]][e];
             col[IA[k]][e] = fma(c, xv, -s * yv);
             col[IB[k]][e] = fma(s, xv, c * yv);
         }
@@ -206,40 +226,52 @@ __device__ __forceinline__ void rot4(double (&col)[8][EPL], double (&nrm)[8], do
 }
 
 // all 16 pairs between block FB (columns FB..FB+3) and block SB
-template <int EPL, int FB, int SB>
-__device__ __forceinline__ void cross_blocks(double (&col)[8][EPL], double (&nrm)[8], double nmax, double& off,
-                                             int lane) {
-    rot4<EPL, FB + 0, SB + 0, FB + 1, SB + 1, FB + 2, SB + 2, FB + 3, SB + 3>(col, nrm, nmax, off, lane);
-    rot4<EPL, FB + 0, SB + 1, FB + 1, SB + 2, FB + 2, SB + 3, FB + 3, SB + 0>(col, nrm, nmax, off, lane);
-    rot4<EPL, FB + 0, SB + 2, FB + 1, SB + 3, FB + 2, SB + 0, FB + 3, SB + 1>(col, nrm, nmax, off, lane);
-    rot4<EPL, FB + 0, SB + 3, FB + 1, SB + 0, FB + 2, SB + 1, FB + 3, SB + 2>(col, nrm, nmax, off, lane);
+template <class T, int EPL, int FB, int SB>
+__device__ __forceinline__ void cross_blocks(T (&col)[8][EPL], T (&nrm)[8], T nmax, T& off, int lane) {
+    rot4<T, EPL, FB + 0, SB + 0, FB + 1, SB + 1, FB + 2, SB + 2, FB + 3, SB + 3>(col, nrm, nmax, off, lane);
+    rot4<T, EPL, FB + 0, SB + 1, FB + 1, SB + 2, FB + 2, SB + 3, FB + 3, SB + 0>(col, nrm, nmax, off, lane);
+    rot4<T, EPL, FB + 0, SB + 2, FB + 1, SB + 3, FB + 2, SB + 0, FB + 3, SB + 1>(col, nrm, nmax, off, lane);
+    rot4<T, EPL, FB + 0, SB + 3, FB + 1, SB + 0, FB + 2, SB + 1, FB + 3, SB + 2>(col, nrm, nmax, off, lane);
 }
 
-template <int EPL, int B>
-__device__ __forceinline__ void put_block(double (*slot)[32 * EPL], double* nslot, const double (&col)[8][EPL],
-                                          const double (&nrm)[8], int lane) {
+// Optional cycle accounting of one warp (build with MUSED_NVCC_EXTRA=-DMUSED_EIG_PROF; tools/k3_prof.sh)
+struct EigProf {
+#ifdef MUSED_EIG_PROF
+    unsigned cross = 0, bar1 = 0, get1 = 0, bar2 = 0, get2 = 0, put = 0, head = 0, t = 0;
+    __device__ __forceinline__ void start() { t = (unsigned)clock(); }
+    __device__ __forceinline__ void lap(unsigned& acc) { const unsigned n = (unsigned)clock(); acc += n - t; t = n; }
+#else
+    __device__ __forceinline__ void start() {}
+    __device__ __forceinline__ void lap(int) {}
+    static constexpr int cross = 0, bar1 = 0, get1 = 0, bar2 = 0, get2 = 0, put = 0, head = 0;
+#endif
+};
+
+// Blocks travel through (distributed) shared memory as arrays of T: slot = EIG_C columns of 32 EPL
+// elements, nslot = their squared norms (the float32 phase uses the first half of each float64 slot).
+template <class T, int EPL, int B>
+__device__ __forceinline__ void put_block(T* slot, T* nslot, const T (&col)[8][EPL], const T (&nrm)[8], int lane) {
 #pragma unroll
     for (int k = 0; k < EIG_C; ++k) {
 #pragma unroll
-        for (int e = 0; e < EPL; ++e) slot[k][lane + 32 * e] = col[B + k][e];
+        for (int e = 0; e < EPL; ++e) slot[k * 32 * EPL + lane + 32 * e] = col[B + k][e];
     }
     if (lane < EIG_C) {
-        double v = nrm[B];
+        T v = nrm[B];
         if (lane == 1) v = nrm[B + 1];
         if (lane == 2) v = nrm[B + 2];
         if (lane == 3) v = nrm[B + 3];
         nslot[lane] = v;
     }
 }
-template <int EPL, int B>
-__device__ __forceinline__ void get_block(uint32_t slot_addr, uint32_t nslot_addr, double (&col)[8][EPL],
-                                          double (&nrm)[8], int lane) {
+template <class T, int EPL, int B>
+__device__ __forceinline__ void get_block(uint32_t slot_addr, uint32_t nslot_addr, T (&col)[8][EPL], T (&nrm)[8], int lane) {
 #pragma unroll
     for (int k = 0; k < EIG_C; ++k) {
 #pragma unroll
         for (int e = 0; e < EPL; ++e)
-            col[B + k][e] = dsmem_ld(slot_addr + (uint32_t)((k * 32 * EPL + lane + 32 * e) * 8));
-        nrm[B + k] = dsmem_ld(nslot_addr + (uint32_t)(k * 8));
+            dsmem_ld_t(slot_addr + (uint32_t)((k * 32 * EPL + lane + 32 * e) * sizeof(T)), col[B + k][e]);
+        dsmem_ld_t(nslot_addr + (uint32_t)(k * sizeof(T)), nrm[B + k]);
     }
 }
 
@@ -248,24 +280,38 @@ __device__ __forceinline__ void get_block(uint32_t slot_addr, uint32_t nslot_add
 // index in the cluster); the same holds on exit.  Rotations never move data: the
 // trade of places is a relabelling, only the blocks that cross a warp boundary
 // travel (one block out, one block in, per round).
-template <int EPL, int FB, int SB>
-__device__ __forceinline__ void jacobi_iteration(EigSmem<EPL>& sm, double (&col)[8][EPL], double (&nrm)[8],
-                                                 double nmax, double& off, int w, int lw, int rank, int lane,
-                                                 int M) {
+template <class T, int EPL, int FB, int SB>
+__device__ __forceinline__ void jacobi_iteration(EigSmem<EPL>& sm, T (&col)[8][EPL], T (&nrm)[8], T nmax, T& off, int w,
+                                                 int lw, int rank, int lane, int M, EigProf& pf) {
+    auto SA = [&](int i) { return reinterpret_cast<T*>(&sm.slotA[i][0][0]); };
+    auto SBk = [&](int i) { return reinterpret_cast<T*>(&sm.slotB[i][0][0]); };
+    auto NA = [&](int i) { return reinterpret_cast<T*>(&sm.normA[i][0]); };
+    auto NB = [&](int i) { return reinterpret_cast<T*>(&sm.normB[i][0]); };
     // even round: positions (2w, 2w+1); afterwards SB is at 2w, FB at 2w+1
-    cross_blocks<EPL, FB, SB>(col, nrm, nmax, off, lane);
+    pf.start();
+    cross_blocks<T, EPL, FB, SB>(col, nrm, nmax, off, lane);
+    pf.lap(pf.cross);
     // odd round: positions (2w+1, 2w+2) = (FB, first block of warp w+1)
-    put_block<EPL, SB>(sm.slotA[lw], sm.normA[lw], col, nrm, lane);
+    put_block<T, EPL, SB>(SA(lw), NA(lw), col, nrm, lane);
+    pf.lap(pf.put);
     cluster_barrier();
+    pf.lap(pf.bar1);
     if (w + 1 < M) {
         const int nlw = (lw + 1) % EIG_WARPS;
         const int nrk = (lw + 1 == EIG_WARPS) ? rank + 1 : rank;
-        get_block<EPL, SB>(dsmem_addr(&sm.slotA[nlw][0][0], nrk), dsmem_addr(&sm.normA[nlw][0], nrk), col, nrm, lane);
-        cross_blocks<EPL, FB, SB>(col, nrm, nmax, off, lane);
+        get_block<T, EPL, SB>(dsmem_addr(SA(nlw), nrk), dsmem_addr(NA(nlw), nrk), col, nrm, lane);
+#ifdef MUSED_EIG_PROF
+        if (col[SB][0] == T(12345.678)) off = T(1);      // consume the loads before the clock is read
+#endif
+        pf.lap(pf.get1);
+        cross_blocks<T, EPL, FB, SB>(col, nrm, nmax, off, lane);
+        pf.lap(pf.cross);
         // afterwards SB is at 2w+1 (stays), FB at 2w+2 (goes to warp w+1)
-        put_block<EPL, FB>(sm.slotB[lw], sm.normB[lw], col, nrm, lane);
+        put_block<T, EPL, FB>(SBk(lw), NB(lw), col, nrm, lane);
+        pf.lap(pf.put);
     }
     cluster_barrier();
+    pf.lap(pf.bar2);
     if (w + 1 == M) {
         // the last warp sat the odd round out: FB is still at 2w+1, register block SB is free
 #pragma unroll
@@ -277,12 +323,16 @@ __device__ __forceinline__ void jacobi_iteration(EigSmem<EPL>& sm, double (&col)
     }
     if (w == 0) {
         // position 0 sat the odd round out, parked in this warp's own slotA
-        get_block<EPL, FB>(dsmem_addr(&sm.slotA[lw][0][0], rank), dsmem_addr(&sm.normA[lw][0], rank), col, nrm, lane);
+        get_block<T, EPL, FB>(dsmem_addr(SA(lw), rank), dsmem_addr(NA(lw), rank), col, nrm, lane);
     } else {
         const int plw = (lw + EIG_WARPS - 1) % EIG_WARPS;
         const int prk = (lw == 0) ? rank - 1 : rank;
-        get_block<EPL, FB>(dsmem_addr(&sm.slotB[plw][0][0], prk), dsmem_addr(&sm.normB[plw][0], prk), col, nrm, lane);
+        get_block<T, EPL, FB>(dsmem_addr(SBk(plw), prk), dsmem_addr(NB(plw), prk), col, nrm, lane);
     }
+#ifdef MUSED_EIG_PROF
+    if (col[FB][0] == T(12345.678)) off = T(1);
+#endif
+    pf.lap(pf.get2);
 }
 
 // Point-to-point variant of the same two rounds (opt-in, MUSED_EIG_P2P=1; measured on B200 at
@@ -325,10 +375,10 @@ template <int EPL, int FB, int SB>
 __device__ __forceinline__ void jacobi_iteration_p2p(EigSmem<EPL>& sm, double (&col)[8][EPL], double (&nrm)[8],
                                                      double nmax, double& off, int w, int lw, int rank, int lane,
                                                      int M, uint32_t parity) {
-    cross_blocks<EPL, FB, SB>(col, nrm, nmax, off, lane);
+    cross_blocks<double, EPL, FB, SB>(col, nrm, nmax, off, lane);
     // SB (now at position 2w) meets position 2w-1 in warp w-1
     if (w == 0) {
-        put_block<EPL, SB>(sm.park, sm.parkn, col, nrm, lane);
+        put_block<double, EPL, SB>(&sm.park[0][0], sm.parkn, col, nrm, lane);
         __syncwarp();
     } else {
         const int plw = (lw + EIG_WARPS - 1) % EIG_WARPS;
@@ -339,7 +389,7 @@ __device__ __forceinline__ void jacobi_iteration_p2p(EigSmem<EPL>& sm, double (&
     if (w + 1 < M) {
         mbar_wait_cluster(&sm.fullA[lw], parity);
         take_block<EPL, SB>(sm.slotA[lw], sm.normA[lw], col, nrm, lane);
-        cross_blocks<EPL, FB, SB>(col, nrm, nmax, off, lane);
+        cross_blocks<double, EPL, FB, SB>(col, nrm, nmax, off, lane);
         // the neighbour's block stays at 2w+1, FB moves on to position 2w+2 (warp w+1)
         const int nlw = (lw + 1) % EIG_WARPS;
         const int nrk = (lw + 1 == EIG_WARPS) ? rank + 1 : rank;
@@ -362,7 +412,76 @@ __device__ __forceinline__ void jacobi_iteration_p2p(EigSmem<EPL>& sm, double (&
     }
 }
 
+// The sweeps of one phase on the register-resident columns.  Returns the sweeps done; `last` = the
+// largest cosine the last started sweep saw at its entry (measured during the sweep before).
+template <class T, int EPL, bool P2P>
+__device__ __forceinline__ int run_sweeps(EigSmem<EPL>& sm, T (&col)[8][EPL], double tol, int max_sweeps, int w, int lw,
+                                          int rank, int lane, int M, uint32_t& itn, double& last, EigProf& pf) {
+    T nrm[8];
+    T off = T(0);
+    int sweeps_done = 0;
+    const uint32_t ro0 = dsmem_addr(sm.red_off, 0), rn0 = dsmem_addr(sm.red_nmax, 0);
+    for (int sweep = 0; sweep < max_sweeps; ++sweep) {
+        T nm = T(0);
+        pf.start();
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            T t = T(0);
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) t = fma(col[k][e], col[k][e], t);
+            nrm[k] = t;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) nrm[k] += __shfl_xor_sync(0xffffffffu, nrm[k], o);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) nm = fmax(nm, nrm[k]);
+        // cluster-wide: largest column norm^2 and the last sweep's largest cosine
+        const double offw = warp_max((double)off);
+        if (lane == 0) {
+            dsmem_st(ro0 + (uint32_t)(w * 8), offw);
+            dsmem_st(rn0 + (uint32_t)(w * 8), (double)nm);
+        }
+        cluster_barrier();
+        double o = 0.0, nmd = 0.0;
+        for (int i = lane; i < M; i += 32) {
+            o = fmax(o, dsmem_ld(ro0 + (uint32_t)(i * 8)));
+            nmd = fmax(nmd, dsmem_ld(rn0 + (uint32_t)(i * 8)));
+        }
+        o = warp_max(o);
+        nm = (T)warp_max(nmd);
+        cluster_barrier();                      // all have read before the arrays are rewritten
+        last = o;
+        if (sweep > 0 && o <= tol) break;
+        off = T(0);
+        // pairs inside each block (three stages of four independent rotations)
+        rot4<T, EPL, 0, 1, 2, 3, 4, 5, 6, 7>(col, nrm, nm, off, lane);
+        rot4<T, EPL, 0, 2, 1, 3, 4, 6, 5, 7>(col, nrm, nm, off, lane);
+        rot4<T, EPL, 0, 3, 1, 2, 4, 7, 5, 6>(col, nrm, nm, off, lane);
+        pf.lap(pf.head);
+        // block pairs: 2M block positions, 2M rounds, two per iteration
+#pragma unroll 1
+        for (int it = 0; it < M; ++it, ++itn) {
+            if constexpr (P2P && sizeof(T) == 8)
+                jacobi_iteration_p2p<EPL, 0, 4>(sm, col, nrm, nm, off, w, lw, rank, lane, M, itn & 1u);
+            else
+                jacobi_iteration<T, EPL, 0, 4>(sm, col, nrm, nm, off, w, lw, rank, lane, M, pf);
+        }
+        sweeps_done = sweep + 1;
+    }
+    return sweeps_done;
+}
+
 // Grid = S * EPL CTAs, cluster = EPL CTAs, EIG_NT threads, dynamic smem = sizeof(EigSmem<EPL>).
+//
+// A.mixed: the rotations of the early sweeps only have to be good enough to converge, so they run in
+// float32 on W32 = G / max|G| (half the issue slots, half the shuffles, a shorter dependent chain per
+// rotation step -- the step latency is what bounds this kernel).  For symmetric G the normalised
+// columns of the converged W are the eigenvectors, so V32 = normalise(W32) needs no accumulation; the
+// float64 phase restarts from W = G V32 (one 2l x 2l x 2l product per instance, G re-read from L2)
+// whose columns are orthogonal to float32 accuracy, runs the usual sweeps (normally one) and leaves
+// column norms = eigenvalues to a RELATIVE ||V32^T V32 - I|| ~ 1e-7, eigenvectors orthonormal to 1e-12.
 template <int EPL, bool P2P>
 __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
     constexpr int N2 = 32 * EPL;
@@ -405,7 +524,6 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
         return r >= A.n_rows || mk[r] != 0;
     };
     double col[8][EPL];
-    double nrm[8];
     {
         const double* G = A.G + (size_t)s * N2 * N2;
 #pragma unroll
@@ -422,55 +540,86 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
         }
     }
 
-    // ---- sweeps -------------------------------------------------------------------------
-    int sweeps_done = 0;
+    int sweeps32 = 0;
     double off = 0.0;
-    const uint32_t ro0 = dsmem_addr(sm.red_off, 0), rn0 = dsmem_addr(sm.red_nmax, 0);
-    for (int sweep = 0; sweep < A.max_sweeps; ++sweep) {
-        double nm = 0.0;
+    EigProf pf;
+    if (A.mixed) {
+        // ---- float32 phase on W32 = Gs / max|Gs| ------------------------------------------
+        double* Gs = A.Gs + (size_t)s * N2 * N2;
+        double gmax = 0.0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) {
+                Gs[(size_t)(8 * w + k) * N2 + lane + 32 * e] = col[k][e];
+                gmax = fmax(gmax, fabs(col[k][e]));
+            }
+        gmax = warp_max(gmax);
+        const uint32_t rn0 = dsmem_addr(sm.red_nmax, 0);
+        if (lane == 0) dsmem_st(rn0 + (uint32_t)(w * 8), gmax);
+        cluster_barrier();
+        gmax = 0.0;
+        for (int i = lane; i < M; i += 32) gmax = fmax(gmax, dsmem_ld(rn0 + (uint32_t)(i * 8)));
+        gmax = warp_max(gmax);
+        cluster_barrier();
+        const double inv = gmax > 0.0 ? 1.0 / gmax : 0.0;
+        float colf[8][EPL];
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) colf[k][e] = (float)(col[k][e] * inv);
+        sweeps32 = run_sweeps<float, EPL, false>(sm, colf, 1e-3, A.max_sweeps, w, lw, rank, lane, M, itn, off, pf);
+#ifdef MUSED_EIG_PROF
+        if (s == 2 && w == 5 && lane == 0 && (A.t_end % 1280ull) == 0ull)
+            printf("K3 prof f32 (%d sweeps) cycles/iteration: cross %u put %u bar1 %u get1 %u bar2 %u get2 %u | head/sweep %u\n", sweeps32,
+                   pf.cross / (sweeps32 * M), pf.put / (sweeps32 * M), pf.bar1 / (sweeps32 * M), pf.get1 / (sweeps32 * M),
+                   pf.bar2 / (sweeps32 * M), pf.get2 / (sweeps32 * M), pf.head / sweeps32);
+        pf = EigProf();
+#endif
+        cluster_barrier();                      // nobody still reads a slot of the exchange
+        // ---- V32 = normalised columns -> this warp's two slots; W = Gs V32 ----------------------
+        double* vsA = &sm.slotA[lw][0][0];       // columns 0..3 of the warp's block, [c][N2]
+        double* vsB = &sm.slotB[lw][0][0];       // columns 4..7
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             double t = 0.0;
 #pragma unroll
-            for (int e = 0; e < EPL; ++e) t = fma(col[k][e], col[k][e], t);
-            nrm[k] = t;
-        }
+            for (int e = 0; e < EPL; ++e) t = fma((double)colf[k][e], (double)colf[k][e], t);
+            t = warp_sum(t);
+            const double rn = t > 0.0 ? rsqrt(t) : 0.0;
+            double* dst = (k < 4 ? vsA : vsB) + (size_t)(k & 3) * N2;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1)
+            for (int e = 0; e < EPL; ++e) dst[lane + 32 * e] = (double)colf[k][e] * rn;
+        }
+        __syncwarp();
 #pragma unroll
-            for (int k = 0; k < 8; ++k) nrm[k] += __shfl_xor_sync(0xffffffffu, nrm[k], o);
+        for (int k = 0; k < 8; ++k)
 #pragma unroll
-        for (int k = 0; k < 8; ++k) nm = fmax(nm, nrm[k]);
-        // cluster-wide: largest column norm^2 and the last sweep's largest cosine
-        off = warp_max(off);
-        if (lane == 0) {
-            dsmem_st(ro0 + (uint32_t)(w * 8), off);
-            dsmem_st(rn0 + (uint32_t)(w * 8), nm);
+            for (int e = 0; e < EPL; ++e) col[k][e] = 0.0;
+#pragma unroll 2
+        for (int kk = 0; kk < N2; ++kk) {
+            double gk[EPL];
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) gk[e] = __ldcg(Gs + (size_t)kk * N2 + lane + 32 * e);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const double v = (c < 4 ? vsA : vsB)[(size_t)(c & 3) * N2 + kk];
+#pragma unroll
+                for (int e = 0; e < EPL; ++e) col[c][e] = fma(gk[e], v, col[c][e]);
+            }
         }
-        cluster_barrier();
-        double o = 0.0;
-        nm = 0.0;
-        for (int i = lane; i < M; i += 32) {
-            o = fmax(o, dsmem_ld(ro0 + (uint32_t)(i * 8)));
-            nm = fmax(nm, dsmem_ld(rn0 + (uint32_t)(i * 8)));
-        }
-        o = warp_max(o);
-        nm = warp_max(nm);
-        cluster_barrier();                      // all have read before the arrays are rewritten
-        if (sweep > 0 && o <= A.tol) break;
-        off = 0.0;
-        // pairs inside each block (three stages of four independent rotations)
-        rot4<EPL, 0, 1, 2, 3, 4, 5, 6, 7>(col, nrm, nm, off, lane);
-        rot4<EPL, 0, 2, 1, 3, 4, 6, 5, 7>(col, nrm, nm, off, lane);
-        rot4<EPL, 0, 3, 1, 2, 4, 7, 5, 6>(col, nrm, nm, off, lane);
-        // block pairs: 2M block positions, 2M rounds, two per iteration
-#pragma unroll 1
-        for (int it = 0; it < M; ++it, ++itn) {
-            if (P2P) jacobi_iteration_p2p<EPL, 0, 4>(sm, col, nrm, nm, off, w, lw, rank, lane, M, itn & 1u);
-            else jacobi_iteration<EPL, 0, 4>(sm, col, nrm, nm, off, w, lw, rank, lane, M);
-        }
-        sweeps_done = sweep + 1;
+        cluster_barrier();                      // the slots go back to the block exchange
     }
+
+    // ---- float64 sweeps -------------------------------------------------------------------
+    int sweeps_done = run_sweeps<double, EPL, P2P>(sm, col, A.tol, A.max_sweeps, w, lw, rank, lane, M, itn, off, pf);
+#ifdef MUSED_EIG_PROF
+    if (s == 2 && w == 5 && lane == 0 && (A.t_end % 1280ull) == 0ull)
+        printf("K3 prof f64 (%d sweeps) cycles/iteration: cross %u put %u bar1 %u get1 %u bar2 %u get2 %u | head/sweep %u\n", sweeps_done,
+               pf.cross / (sweeps_done * M), pf.put / (sweeps_done * M), pf.bar1 / (sweeps_done * M), pf.get1 / (sweeps_done * M),
+               pf.bar2 / (sweeps_done * M), pf.get2 / (sweeps_done * M), pf.head / sweeps_done);
+#endif
+    sweeps_done += 100 * sweeps32;
 
     // ---- eigenvalues per column id, replicated into every CTA ---------------------------
     double lamv[8];
