@@ -287,31 +287,38 @@ __device__ __forceinline__ void jacobi_iteration(EigSmem<EPL>& sm, T (&col)[8][E
     auto SBk = [&](int i) { return reinterpret_cast<T*>(&sm.slotB[i][0][0]); };
     auto NA = [&](int i) { return reinterpret_cast<T*>(&sm.normA[i][0]); };
     auto NB = [&](int i) { return reinterpret_cast<T*>(&sm.normB[i][0]); };
-    // even round: positions (2w, 2w+1); afterwards SB is at 2w, FB at 2w+1
-    pf.start();
-    cross_blocks<T, EPL, FB, SB>(col, nrm, nmax, off, lane);
-    pf.lap(pf.cross);
-    // odd round: positions (2w+1, 2w+2) = (FB, first block of warp w+1)
-    put_block<T, EPL, SB>(SA(lw), NA(lw), col, nrm, lane);
-    pf.lap(pf.put);
-    cluster_barrier();
-    pf.lap(pf.bar1);
-    if (w + 1 < M) {
-        const int nlw = (lw + 1) % EIG_WARPS;
-        const int nrk = (lw + 1 == EIG_WARPS) ? rank + 1 : rank;
-        get_block<T, EPL, SB>(dsmem_addr(SA(nlw), nrk), dsmem_addr(NA(nlw), nrk), col, nrm, lane);
+    // Two rounds, ONE copy of the sixteen-rotation code (a 2-trip loop: the loop body is what has to stay in
+    // the instruction cache -- "no instruction" stalls were 12% of this kernel with two inlined copies).
+    // Trip 0, even round: positions (2w, 2w+1); afterwards SB is at 2w, FB at 2w+1; SB leaves for warp w-1's
+    // odd round and warp w+1's SB arrives.  Trip 1, odd round: positions (2w+1, 2w+2) = (FB, first block of
+    // warp w+1); afterwards that block stays at 2w+1 and FB moves on to warp w+1.
+    const bool inner = w + 1 < M;
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+        pf.start();
+        if (half == 0 || inner) {
+            cross_blocks<T, EPL, FB, SB>(col, nrm, nmax, off, lane);
+            pf.lap(pf.cross);
+            if (half == 0) put_block<T, EPL, SB>(SA(lw), NA(lw), col, nrm, lane);
+            else put_block<T, EPL, FB>(SBk(lw), NB(lw), col, nrm, lane);
+            pf.lap(pf.put);
+        }
+        cluster_barrier();
+        if (half == 0) {
+            pf.lap(pf.bar1);
+            if (inner) {
+                const int nlw = (lw + 1) % EIG_WARPS;
+                const int nrk = (lw + 1 == EIG_WARPS) ? rank + 1 : rank;
+                get_block<T, EPL, SB>(dsmem_addr(SA(nlw), nrk), dsmem_addr(NA(nlw), nrk), col, nrm, lane);
+            }
 #ifdef MUSED_EIG_PROF
-        if (col[SB][0] == T(12345.678)) off = T(1);      // consume the loads before the clock is read
+            if (col[SB][0] == T(12345.678)) off = T(1);      // consume the loads before the clock is read
 #endif
-        pf.lap(pf.get1);
-        cross_blocks<T, EPL, FB, SB>(col, nrm, nmax, off, lane);
-        pf.lap(pf.cross);
-        // afterwards SB is at 2w+1 (stays), FB at 2w+2 (goes to warp w+1)
-        put_block<T, EPL, FB>(SBk(lw), NB(lw), col, nrm, lane);
-        pf.lap(pf.put);
+            pf.lap(pf.get1);
+        } else {
+            pf.lap(pf.bar2);
+        }
     }
-    cluster_barrier();
-    pf.lap(pf.bar2);
     if (w + 1 == M) {
         // the last warp sat the odd round out: FB is still at 2w+1, register block SB is free
 #pragma unroll
