@@ -179,6 +179,27 @@ __device__ __forceinline__ void jacobi_angle(T g, T nx, T ny, T nmax, T& off, T&
     my = fma(ss, nx, fma(cc, ny, cs2));      // |s x + c y|^2
 }
 
+// packed float32 pairs (FFMA2 / FMUL2 on sm_100): the float32 phase is bound by issued instructions, the
+// two halves of a register pair ride one instruction; element-wise results equal the scalar fmaf / fmul
+__device__ __forceinline__ unsigned long long pk2(float lo, float hi) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void upk2(unsigned long long v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigned long long b) {
+    unsigned long long r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
 // Four independent rotations (column ids A_k, B_k of the warp's eight columns).
 // The four inner products are reduced together (6 shuffles instead of 20: after
 // the xor-16 and xor-8 steps lane group q = lane/8 owns product q), group q
@@ -190,13 +211,23 @@ __device__ __forceinline__ void rot4(T (&col)[8][EPL], T (&nrm)[8], T nmax, T& o
     T g[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        T g0 = T(0), g1 = T(0);
+        if constexpr (sizeof(T) == 4 && EPL % 2 == 0) {
+            unsigned long long acc = 0ull;
 #pragma unroll
-        for (int e = 0; e < EPL; e += 2) {
-            g0 = fma(col[IA[k]][e], col[IB[k]][e], g0);
-            if (e + 1 < EPL) g1 = fma(col[IA[k]][e + 1], col[IB[k]][e + 1], g1);
+            for (int e = 0; e < EPL; e += 2)
+                acc = fma2(pk2(col[IA[k]][e], col[IA[k]][e + 1]), pk2(col[IB[k]][e], col[IB[k]][e + 1]), acc);
+            float lo, hi;
+            upk2(acc, lo, hi);
+            g[k] = lo + hi;
+        } else {
+            T g0 = T(0), g1 = T(0);
+#pragma unroll
+            for (int e = 0; e < EPL; e += 2) {
+                g0 = fma(col[IA[k]][e], col[IB[k]][e], g0);
+                if (e + 1 < EPL) g1 = fma(col[IA[k]][e + 1], col[IB[k]][e + 1], g1);
+            }
+            g[k] = g0 + g1;
         }
-        g[k] = g0 + g1;
     }
     const bool h16 = (lane & 16) != 0, h8 = (lane & 8) != 0;
     T k0 = sel(h16, g[2], g[0]) + __shfl_xor_sync(0xffffffffu, sel(h16, g[0], g[2]), 16);
@@ -216,11 +247,22 @@ __device__ __forceinline__ void rot4(T (&col)[8][EPL], T (&nrm)[8], T nmax, T& o
         const T s = __shfl_sync(0xffffffffu, sq, 8 * k);
         nrm[IA[k]] = __shfl_sync(0xffffffffu, mxq, 8 * k);
         nrm[IB[k]] = __shfl_sync(0xffffffffu, myq, 8 * k);
+        if constexpr (sizeof(T) == 4 && EPL % 2 == 0) {
+            const unsigned long long c2 = pk2(c, c), s2 = pk2(s, s), ns2 = pk2(-s, -s);
 #pragma unroll
-        for (int e = 0; e < EPL; ++e) {
-            const T xv = col[IA[k]][e], yv = col[IB[k]][e];
-            col[IA[k]][e] = fma(c, xv, -s * yv);
-            col[IB[k]][e] = fma(s, xv, c * yv);
+            for (int e = 0; e < EPL; e += 2) {
+                const unsigned long long X = pk2(col[IA[k]][e], col[IA[k]][e + 1]);
+                const unsigned long long Y = pk2(col[IB[k]][e], col[IB[k]][e + 1]);
+                upk2(fma2(c2, X, mul2(ns2, Y)), col[IA[k]][e], col[IA[k]][e + 1]);
+                upk2(fma2(s2, X, mul2(c2, Y)), col[IB[k]][e], col[IB[k]][e + 1]);
+            }
+        } else {
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) {
+                const T xv = col[IA[k]][e], yv = col[IB[k]][e];
+                col[IA[k]][e] = fma(c, xv, -s * yv);
+                col[IB[k]][e] = fma(s, xv, c * yv);
+            }
         }
     }
 }
