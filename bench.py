@@ -412,19 +412,23 @@ def run_ours(args, rank, local_rank, world):
         dur_s = km[dom] / chunks * 1e-3
         achieved = bytes_per_row * rows_per_launch / dur_s / 1e9
         # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full of this workload
-        # (profiles/r01_ncu_full_summary.csv); the FD state is L2-resident, hence far below the algorithmic bytes
-        ncu_traffic = {"K3_eig": 6378240, "K2_gram": 13872640 + 1511680, "K1_stage": 33566976 + 11879680,
+        # (profiles/r01_ncu_full_summary.csv, K3: profiles/r01_ncu_k3_mixed_stalls.csv); the FD state is L2-resident,
+        # hence far below the algorithmic bytes
+        ncu_traffic = {"K3_eig": 6439424, "K2_gram": 13872640 + 1511680, "K1_stage": 33566976 + 11879680,
                        "K5_book": 127232, "K4_rotate": 16892416 + 84224}
         roofline = {"bound": "hbm", "kernel": {"K1_stage": "k_bstage", "K5_book": "k_bbook", "K2_gram": "k_gram_tc",
                                                 "K3_eig": "k_eig_jacobi", "K4_rotate": "k_rotate_tc"}[dom],
                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": ncu_traffic.get(dom),
-                    "fp64_pipe_active_pct": 30.7 if dom == "K3_eig" else None,
+                    "issue_active_pct": 29.7 if dom == "K3_eig" else None,
+                    "cycles_per_issued_instruction": 3.37 if dom == "K3_eig" else None,
                     "peak_source": how, "algorithmic_bytes_per_row": bytes_per_row,
                     "rows_per_launch": rows_per_launch, "avg_launch_ms": km[dom] / chunks,
                     "share_of_step": km[dom] / main_res["ms_total"],
-                    "note": "dominant kernel is the batched float64 eigensolve (FP64-issue / cluster-barrier bound, "
-                            "no HBM or tensor roofline applies); bytes are SURVEY 8(d)'s per-row figure"}
+                    "note": "dominant kernel is the batched mixed-precision Jacobi eigensolve: one warp per scheduler, "
+                            "3.4 cycles per issued instruction (dependency wait, shuffle/MUFU scoreboard, instruction "
+                            "fetch, cluster barrier) -- a dependent-issue chain, no HBM or tensor roofline applies; "
+                            "bytes are SURVEY 8(d)'s per-row figure"}
         n2 = 2 * ELL
         us = {k: v / chunks * 1e3 for k, v in km.items()}
         kernels = {
@@ -435,7 +439,7 @@ def run_ours(args, rank, local_rank, world):
                         "achieved_TFLOPs_dense": S * 2.0 * n2 * n2 * D / (us["K2_gram"] * 1e-6) / 1e12,
                         "issued_TFLOPs_3xTF32": 3 * S * 2.0 * n2 * n2 * D / (us["K2_gram"] * 1e-6) / 1e12,
                         "peak_bf16_TFLOPs": tpeak, "note": "kind::tf32 runs at half the bf16 rate; 3 passes"},
-            "K3_eig": {"us_per_chunk": us["K3_eig"], "bound": "fp64-issue/barrier",
+            "K3_eig": {"us_per_chunk": us["K3_eig"], "bound": "dependent-issue chain / cluster barrier",
                        "share_of_step": km["K3_eig"] / main_res["ms_total"]},
             "K4_rotate": {"us_per_chunk": us["K4_rotate"], "bound": "tensor",
                           "achieved_TFLOPs_dense": S * 2.0 * ELL * n2 * D / (us["K4_rotate"] * 1e-6) / 1e12,
@@ -478,7 +482,7 @@ def run_ours(args, rank, local_rank, world):
     line = {
         "metric": METRIC, "value": main_res["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": main_res["ms_total"] / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32 rows, 3xTF32 products, f64 eigensolve"
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32 rows, 3xTF32 products, f32+f64 eigensolve"
         if args.schedule == "batched" else "f64", "data": "synthetic",
         "config": {"workload": "SWFD d=1024 l=128 N=10000 low-rank+noise stream + cosine assign k=150 (configs[1])",
                    "schedule": args.schedule, "levels": S // 2, "fd_instances": S, "rows_per_step": WIN,

@@ -89,12 +89,16 @@ __global__ void __launch_bounds__(256) k_bstage_v4(const float* __restrict__ in,
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_bbook(BDev D, int n, unsigned long long t_a) {
     __shared__ int raw_row[BS_MAX_ELL], raw_slot[BS_MAX_ELL];
+    __shared__ unsigned char is_raw[BS_MAX_ELL];
     __shared__ int n_raw_s, do_reset;
     const int s = blockIdx.x;
     BSlot& sl = D.slots[s];
     const unsigned long long t_b = t_a + (unsigned long long)n - 1ull;
     unsigned long long* qs = D.ringS + (size_t)s * D.capn;
     unsigned long long* qt = D.ringT + (size_t)s * D.capn;
+    // routing test of every row in parallel (seq_based_swfd.py:76-77); the serial part below only walks flags
+    for (int r = threadIdx.x; r < n; r += 256) is_raw[r] = D.norm2[D.x0 + r] >= sl.error ? 1 : 0;
+    __syncthreads();
     if (threadIdx.x == 0) {
         int reset = 0;
         const unsigned long long p = t_a / D.N;
@@ -118,9 +122,8 @@ __global__ void __launch_bounds__(256) k_bbook(BDev D, int n, unsigned long long
         }
         int nr = 0;
         unsigned long long last = sl.last_dump;
-        const double thr = sl.error;
         for (int r = 0; r < n; ++r) {
-            if (D.norm2[D.x0 + r] >= thr) {        // :76-77 -> SlidingWindowFD.append (:56-80)
+            if (is_raw[r]) {                       // -> SlidingWindowFD.append (:56-80)
                 if (len == D.capn) { head = (head + 1) % D.capn; --len; sl.overflow += 1; }
                 const int tail = (head + len) % D.capn;
                 qs[tail] = last;

@@ -30,7 +30,8 @@ class SeqBasedSWFD:
           "batched"    one tensor-core Gram + eigensolve + rotate per chunk of
                        batch_rows (default sketch_dim) rows, all directions with
                        sigma^2 >= threshold dumped per chunk (the throughput path;
-                       semantics stated in oracle/swfd_batched_oracle.py).
+                       semantics stated in oracle/swfd_batched_oracle.py); sketch_dim
+                       2..128, any d > sketch_dim.
         """
         self.N = np.uint64(N)
         self.d = int(d)
