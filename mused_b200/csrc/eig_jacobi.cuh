@@ -590,7 +590,8 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
     }
 
     int sweeps32 = 0;
-    double off = 0.0;
+    double off = 0.0, fro = 0.0;
+    bool from_gram = !A.mixed;              // the float64 sweeps start from G itself
     EigProf pf;
     if (A.mixed) {
         // ---- float32 phase on W32 = Gs / max|Gs| ------------------------------------------
@@ -602,14 +603,27 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
             for (int e = 0; e < EPL; ++e) {
                 Gs[(size_t)(8 * w + k) * N2 + lane + 32 * e] = col[k][e];
                 gmax = fmax(gmax, fabs(col[k][e]));
+                fro = fma(col[k][e], col[k][e], fro);
             }
         gmax = warp_max(gmax);
+        fro = warp_sum(fro);
         const uint32_t rn0 = dsmem_addr(sm.red_nmax, 0);
-        if (lane == 0) dsmem_st(rn0 + (uint32_t)(w * 8), gmax);
-        cluster_barrier();
-        gmax = 0.0;
-        for (int i = lane; i < M; i += 32) gmax = fmax(gmax, dsmem_ld(rn0 + (uint32_t)(i * 8)));
-        gmax = warp_max(gmax);
+        {
+            const uint32_t rf0 = dsmem_addr(sm.red_off, 0);
+            if (lane == 0) {
+                dsmem_st(rn0 + (uint32_t)(w * 8), gmax);
+                dsmem_st(rf0 + (uint32_t)(w * 8), fro);
+            }
+            cluster_barrier();
+            gmax = 0.0;
+            fro = 0.0;
+            for (int i = lane; i < M; i += 32) {
+                gmax = fmax(gmax, dsmem_ld(rn0 + (uint32_t)(i * 8)));
+                fro += dsmem_ld(rf0 + (uint32_t)(i * 8));
+            }
+            gmax = warp_max(gmax);
+            fro = warp_sum(fro);                 // ||Gs||_F^2 = sum of squared eigenvalues: the check after the solve
+        }
         cluster_barrier();
         const double inv = gmax > 0.0 ? 1.0 / gmax : 0.0;
         float colf[8][EPL];
@@ -626,71 +640,131 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
         pf = EigProf();
 #endif
         cluster_barrier();                      // nobody still reads a slot of the exchange
-        // ---- V32 = normalised columns -> this warp's two slots; W = Gs V32 ----------------------
-        double* vsA = &sm.slotA[lw][0][0];       // columns 0..3 of the warp's block, [c][N2]
-        double* vsB = &sm.slotB[lw][0][0];       // columns 4..7
+        // ---- is every column's direction trustworthy? ------------------------------------------
+        // A column whose norm fell to the float32 round-off level of the largest one (numerically rank-deficient
+        // G: exact low rank, repeated rows) points nowhere in particular; normalising it would put a unit vector
+        // that is NOT orthogonal to the others into V32 and the restart W = G V32 would no longer have the
+        // singular values of G.  Columns that are exactly zero (masked rows, empty sketch rows) are harmless.
+        // With the smallest non-zero column at >= 1e-3 of the largest, a direction error d <= 1e-3 of a small
+        // column perturbs a large eigenvalue by d^2 / 2.  Otherwise this instance takes the float64 sweeps from G.
+        double tk[8];
+        double tmax = 0.0, tmin = DBL_MAX;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             double t = 0.0;
 #pragma unroll
             for (int e = 0; e < EPL; ++e) t = fma((double)colf[k][e], (double)colf[k][e], t);
             t = warp_sum(t);
-            const double rn = t > 0.0 ? rsqrt(t) : 0.0;
-            double* dst = (k < 4 ? vsA : vsB) + (size_t)(k & 3) * N2;
-#pragma unroll
-            for (int e = 0; e < EPL; ++e) dst[lane + 32 * e] = (double)colf[k][e] * rn;
+            tk[k] = t;
+            tmax = fmax(tmax, t);
+            if (t > 0.0) tmin = fmin(tmin, t);
         }
-        __syncwarp();
+        {
+            const uint32_t ro0 = dsmem_addr(sm.red_off, 0);
+            if (lane == 0) {
+                dsmem_st(rn0 + (uint32_t)(w * 8), tmax);
+                dsmem_st(ro0 + (uint32_t)(w * 8), -tmin);
+            }
+            cluster_barrier();
+            double a = 0.0, b = -DBL_MAX;
+            for (int i = lane; i < M; i += 32) {
+                a = fmax(a, dsmem_ld(rn0 + (uint32_t)(i * 8)));
+                b = fmax(b, dsmem_ld(ro0 + (uint32_t)(i * 8)));
+            }
+            tmax = warp_max(a);
+            tmin = -warp_max(b);
+            cluster_barrier();
+        }
+        if (tmin < 1e-10 * tmax) {
+            // numerically rank-deficient: float64 sweeps from the Gram itself
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+#pragma unroll
+                for (int e = 0; e < EPL; ++e) col[k][e] = __ldcg(Gs + (size_t)(8 * w + k) * N2 + lane + 32 * e);
+            sweeps32 += 50;                     // flag in BSlot::sweeps
+            from_gram = true;
+        } else {
+            // ---- V32 = normalised columns -> this warp's two slots; W = Gs V32 ------------------
+            double* vsA = &sm.slotA[lw][0][0];       // columns 0..3 of the warp's block, [c][N2]
+            double* vsB = &sm.slotB[lw][0][0];       // columns 4..7
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const double rn = tk[k] > 0.0 ? rsqrt(tk[k]) : 0.0;
+                double* dst = (k < 4 ? vsA : vsB) + (size_t)(k & 3) * N2;
+#pragma unroll
+                for (int e = 0; e < EPL; ++e) dst[lane + 32 * e] = (double)colf[k][e] * rn;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+#pragma unroll
+                for (int e = 0; e < EPL; ++e) col[k][e] = 0.0;
+#pragma unroll 2
+            for (int kk = 0; kk < N2; ++kk) {
+                double gk[EPL];
+#pragma unroll
+                for (int e = 0; e < EPL; ++e) gk[e] = __ldcg(Gs + (size_t)kk * N2 + lane + 32 * e);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const double v = (c < 4 ? vsA : vsB)[(size_t)(c & 3) * N2 + kk];
+#pragma unroll
+                    for (int e = 0; e < EPL; ++e) col[c][e] = fma(gk[e], v, col[c][e]);
+                }
+            }
+            cluster_barrier();                  // the slots go back to the block exchange
+        }
+    }
+
+    // ---- float64 sweeps; eigenvalues per column id, replicated into every CTA ------------------------
+    // After a mixed-precision solve the result is CHECKED: sum of lambda^2 must equal ||G||_F^2 (1e-6
+    // relative; a restart basis V32 that was not orthonormal fails it by orders of magnitude); a failed
+    // check repeats the float64 sweeps from G itself.
+    int sweeps_done = 0;
+    double lamv[8];
+#pragma unroll 1
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        sweeps_done += run_sweeps<double, EPL, P2P>(sm, col, A.tol, A.max_sweeps, w, lw, rank, lane, M, itn, off, pf);
+#ifdef MUSED_EIG_PROF
+        if (s == 2 && w == 5 && lane == 0 && (A.t_end % 1280ull) == 0ull)
+            printf("K3 prof f64 (%d sweeps) cycles/iteration: cross %u put %u bar1 %u get1 %u bar2 %u get2 %u | head/sweep %u\n", sweeps_done,
+                   pf.cross / (sweeps_done * M), pf.put / (sweeps_done * M), pf.bar1 / (sweeps_done * M), pf.get1 / (sweeps_done * M),
+                   pf.bar2 / (sweeps_done * M), pf.get2 / (sweeps_done * M), pf.head / sweeps_done);
+#endif
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            double t = 0.0;
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) t = fma(col[k][e], col[k][e], t);
+            lamv[k] = t;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) lamv[k] += __shfl_xor_sync(0xffffffffu, lamv[k], o);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) lamv[k] = sqrt(lamv[k]);
+        if (lane < EPL) {
+            const uint32_t dst = dsmem_addr(sm.lam, lane);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) dsmem_st(dst + (uint32_t)((8 * w + k) * 8), lamv[k]);
+        }
+        cluster_barrier();
+        if (from_gram) break;
+        double l2 = 0.0;
+        for (int i = lane; i < N2; i += 32) l2 = fma(sm.lam[i], sm.lam[i], l2);
+        l2 = warp_sum(l2);
+        if (fabs(l2 - fro) <= 1e-6 * fro) break;
+        const double* Gs = A.Gs + (size_t)s * N2 * N2;
 #pragma unroll
         for (int k = 0; k < 8; ++k)
 #pragma unroll
-            for (int e = 0; e < EPL; ++e) col[k][e] = 0.0;
-#pragma unroll 2
-        for (int kk = 0; kk < N2; ++kk) {
-            double gk[EPL];
-#pragma unroll
-            for (int e = 0; e < EPL; ++e) gk[e] = __ldcg(Gs + (size_t)kk * N2 + lane + 32 * e);
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const double v = (c < 4 ? vsA : vsB)[(size_t)(c & 3) * N2 + kk];
-#pragma unroll
-                for (int e = 0; e < EPL; ++e) col[c][e] = fma(gk[e], v, col[c][e]);
-            }
-        }
-        cluster_barrier();                      // the slots go back to the block exchange
+            for (int e = 0; e < EPL; ++e) col[k][e] = __ldcg(Gs + (size_t)(8 * w + k) * N2 + lane + 32 * e);
+        from_gram = true;
+        sweeps32 += 70;                         // flag in BSlot::sweeps: the check failed
+        cluster_barrier();                      // everyone has read sm.lam
     }
-
-    // ---- float64 sweeps -------------------------------------------------------------------
-    int sweeps_done = run_sweeps<double, EPL, P2P>(sm, col, A.tol, A.max_sweeps, w, lw, rank, lane, M, itn, off, pf);
-#ifdef MUSED_EIG_PROF
-    if (s == 2 && w == 5 && lane == 0 && (A.t_end % 1280ull) == 0ull)
-        printf("K3 prof f64 (%d sweeps) cycles/iteration: cross %u put %u bar1 %u get1 %u bar2 %u get2 %u | head/sweep %u\n", sweeps_done,
-               pf.cross / (sweeps_done * M), pf.put / (sweeps_done * M), pf.bar1 / (sweeps_done * M), pf.get1 / (sweeps_done * M),
-               pf.bar2 / (sweeps_done * M), pf.get2 / (sweeps_done * M), pf.head / sweeps_done);
-#endif
     sweeps_done += 100 * sweeps32;
 
-    // ---- eigenvalues per column id, replicated into every CTA ---------------------------
-    double lamv[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        double t = 0.0;
-#pragma unroll
-        for (int e = 0; e < EPL; ++e) t = fma(col[k][e], col[k][e], t);
-        lamv[k] = t;
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1)
-#pragma unroll
-        for (int k = 0; k < 8; ++k) lamv[k] += __shfl_xor_sync(0xffffffffu, lamv[k], o);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) lamv[k] = sqrt(lamv[k]);
-    if (lane < EPL) {
-        const uint32_t dst = dsmem_addr(sm.lam, lane);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) dsmem_st(dst + (uint32_t)((8 * w + k) * 8), lamv[k]);
-    }
-    cluster_barrier();
     // rank (descending, ties by column id) of my eight columns
     int rk[8];
 #pragma unroll
