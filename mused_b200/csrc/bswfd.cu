@@ -476,6 +476,7 @@ static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t 
     A.tol = 1e-3;          // quadratic phase: the sweep that measures <= 1e-3 leaves ~1e-6 (Gram accuracy)
     A.max_sweeps = 24;
     A.mixed = mixed;
+    A.small_col = getenv("MUSED_EIG_SMALLCOL") ? atof(getenv("MUSED_EIG_SMALLCOL")) : 1e-14;
     A.Gs = E.D.Gs;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(E.D.S * EPL));

@@ -53,6 +53,7 @@ struct EigArgs {
     unsigned long long* ringT;
     double tol;              // convergence: max |x.y| / (|x||y|)
     int max_sweeps;
+    double small_col;        // mixed: smallest trusted (column norm / largest column norm)^2 after the float32 phase
     int mixed;               // 1 = float32 sweeps first, then W = G V32 and float64 sweeps (see k_eig_jacobi)
     double* Gs;              // [S][n2][n2] scratch: the symmetrised, masked Gram (mixed only)
 };
@@ -645,8 +646,9 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
         // G: exact low rank, repeated rows) points nowhere in particular; normalising it would put a unit vector
         // that is NOT orthogonal to the others into V32 and the restart W = G V32 would no longer have the
         // singular values of G.  Columns that are exactly zero (masked rows, empty sketch rows) are harmless.
-        // With the smallest non-zero column at >= 1e-3 of the largest, a direction error d <= 1e-3 of a small
-        // column perturbs a large eigenvalue by d^2 / 2.  Otherwise this instance takes the float64 sweeps from G.
+        // A direction error d of a small column perturbs the large eigenvalues by d^2 / 2 (relative).  Columns
+        // below 1e-7 of the largest are certainly noise: that instance takes the float64 sweeps from G at once;
+        // anything in between is caught by the check of the finished solve below (sum of lambda^2 = ||G||_F^2).
         double tk[8];
         double tmax = 0.0, tmin = DBL_MAX;
 #pragma unroll
@@ -675,7 +677,7 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
             tmin = -warp_max(b);
             cluster_barrier();
         }
-        if (tmin < 1e-10 * tmax) {
+        if (tmin < A.small_col * tmax) {
             // numerically rank-deficient: float64 sweeps from the Gram itself
 #pragma unroll
             for (int k = 0; k < 8; ++k)
