@@ -786,6 +786,16 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
     }
     cluster_barrier();
     const double cut = sm.cut;
+    // Directions below the float64 round-off of the largest eigenvalue have no usable eigenvector: a column
+    // w = G v of a (numerically) null direction v is rounding residue that lies IN the range of G, so
+    // u = w / |w| is a unit vector with u^T G u of the order of the significant eigenvalues, and
+    // sqrt((lambda - cut) / lambda) of two residues can be anything in [0, 1]: the rotate would write a row
+    // of real energy into the sketch (seen after a chunk of identical rows, whose Gram is EXACTLY rank
+    // deficient; LAPACK's null singular vectors times sqrt(~0) give zero rows).  Such rows are zero here too.
+    double lam_max = 0.0;
+    for (int i = lane; i < N2; i += 32) lam_max = fmax(lam_max, sm.lam[i]);
+    lam_max = warp_max(lam_max);
+    const double lam_floor = 1e-10 * lam_max;
 
     // ---- outputs -------------------------------------------------------------------------
     const int src_plane = sl.cur;
@@ -796,7 +806,7 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
         const int r = rk[k];
         if (r >= ELL) continue;
         const double lam = lamv[k];
-        const double s2v = (r < A.ell_l) ? fmax(lam - cut, 0.0) : 0.0;
+        const double s2v = (r < A.ell_l && lam > lam_floor) ? fmax(lam - cut, 0.0) : 0.0;
         const double coef = (lam > 0.0 && s2v > 0.0) ? sqrt(s2v / lam) / lam : 0.0;
 #pragma unroll
         for (int e = 0; e < EPL; ++e) {
