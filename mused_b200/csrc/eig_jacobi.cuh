@@ -53,6 +53,7 @@ struct EigArgs {
     unsigned long long* ringT;
     double tol;              // convergence: max |x.y| / (|x||y|)
     int max_sweeps;
+    double tol32;            // mixed: the float32 phase ends after the sweep that measured a largest cosine <= tol32
     double small_col;        // mixed: smallest trusted (column norm / largest column norm)^2 after the float32 phase
     int mixed;               // 1 = float32 sweeps first, then W = G V32 and float64 sweeps (see k_eig_jacobi)
     double* Gs;              // [S][n2][n2] scratch: the symmetrised, masked Gram (mixed only)
@@ -632,7 +633,7 @@ __global__ void __launch_bounds__(EIG_NT, 1) k_eig_jacobi(EigArgs A) {
         for (int k = 0; k < 8; ++k)
 #pragma unroll
             for (int e = 0; e < EPL; ++e) colf[k][e] = (float)(col[k][e] * inv);
-        sweeps32 = run_sweeps<float, EPL, false>(sm, colf, 1e-3, A.max_sweeps, w, lw, rank, lane, M, itn, off, pf);
+        sweeps32 = run_sweeps<float, EPL, false>(sm, colf, A.tol32, A.max_sweeps, w, lw, rank, lane, M, itn, off, pf);
 #ifdef MUSED_EIG_PROF
         if (s == 2 && w == 5 && lane == 0 && (A.t_end % 1280ull) == 0ull)
             printf("K3 prof f32 (%d sweeps) cycles/iteration: cross %u put %u bar1 %u get1 %u bar2 %u get2 %u | head/sweep %u\n", sweeps32,
