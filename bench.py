@@ -414,20 +414,20 @@ def run_ours(args, rank, local_rank, world):
         # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full of this workload
         # (profiles/r01_ncu_full_summary.csv, K3: profiles/r01_ncu_k3_mixed_stalls.csv); the FD state is L2-resident,
         # hence far below the algorithmic bytes
-        ncu_traffic = {"K3_eig": 6439424, "K2_gram": 13872640 + 1511680, "K1_stage": 33566976 + 11879680,
+        ncu_traffic = {"K3_eig": 6481920, "K2_gram": 13872640 + 1511680, "K1_stage": 33566976 + 11879680,
                        "K5_book": 127232, "K4_rotate": 16892416 + 84224}
         roofline = {"bound": "hbm", "kernel": {"K1_stage": "k_bstage", "K5_book": "k_bbook", "K2_gram": "k_gram_tc",
                                                 "K3_eig": "k_eig_jacobi", "K4_rotate": "k_rotate_tc"}[dom],
                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": ncu_traffic.get(dom),
-                    "issue_active_pct": 29.7 if dom == "K3_eig" else None,
-                    "cycles_per_issued_instruction": 3.37 if dom == "K3_eig" else None,
+                    "issue_active_pct": 23.6 if dom == "K3_eig" else None,
+                    "cycles_per_issued_instruction": 4.23 if dom == "K3_eig" else None,
                     "peak_source": how, "algorithmic_bytes_per_row": bytes_per_row,
                     "rows_per_launch": rows_per_launch, "avg_launch_ms": km[dom] / chunks,
                     "share_of_step": km[dom] / main_res["ms_total"],
                     "note": "dominant kernel is the batched mixed-precision Jacobi eigensolve: one warp per scheduler, "
-                            "3.4 cycles per issued instruction (dependency wait, shuffle/MUFU scoreboard, instruction "
-                            "fetch, cluster barrier) -- a dependent-issue chain, no HBM or tensor roofline applies; "
+                            "4.2 cycles per issued instruction (dependency wait 1.5, shuffle/MUFU scoreboard 0.65, "
+                            "cluster barrier + fence 0.64, DSMEM 0.19, instruction fetch 0.16) -- a dependent-issue chain, no HBM or tensor roofline applies; "
                             "bytes are SURVEY 8(d)'s per-row figure"}
         n2 = 2 * ELL
         us = {k: v / chunks * 1e3 for k, v in km.items()}
