@@ -62,7 +62,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             sys.stderr.write(out)
         if p.returncode != 0:
             raise RuntimeError("nvcc failed on %s" % s)
-    cmd = [nvcc, "-shared", "-o", LIB, *objs, "-lcudart", "-lcuda"]
+    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB, *objs, "-lcudart", "-lcuda"]
     subprocess.run(cmd, check=True)
     with open(STAMP, "w") as f:
         f.write(dig)

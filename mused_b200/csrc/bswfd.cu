@@ -3,7 +3,7 @@
 //   K1  k_bstage    rows (any dtype) -> TF32 hi/lo planes of the shared chunk + ||x||^2
 //   K5  k_bbook     period swap, snapshot expiry / cap trim, raw-row snapshots, masks
 //   K2  k_gram_tc   G = [sketch; chunk][sketch; chunk]^T          (tcgen05, gram_tc.cuh)
-//   K3  k_eig_jacobi  eig(G), shrink, dump decisions                (eig_jacobi.cuh)
+//   K3  k_eig_jacobi  eig(G), shrink, dump decisions                (eig_smem.cuh)
 //   K4  k_rotate_tc sketch' = T [sketch; chunk] (tcgen05, rotate_tc.cuh), dumped rows -> snapshot ring
 // with no host synchronisation between chunks.  The schedule and its arithmetic
 // are stated in oracle/swfd_batched_oracle.py; reference lines:
@@ -15,6 +15,7 @@
 
 #include "bswfd.h"
 #include "gram_tc.cuh"
+#include "eig_smem.cuh"
 #include "rotate_tc.cuh"
 
 namespace mused {
@@ -427,11 +428,7 @@ void bengine_destroy(BEngine* E) {
 template <int N2>
 static int launch_gram(BEngine& E, cudaStream_t st) {
     using C = GramCfg<N2>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        MUSED_CUDA(cudaFuncSetAttribute(k_gram_tc<N2>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-        attr_set = true;
-    }
+    MUSED_SMEM_ATTR(k_gram_tc<N2>, C::SMEM_BYTES);
     GramArgs A;
     A.slots = E.D.slots;
     A.Gp = E.D.Gp;
@@ -446,17 +443,9 @@ static int launch_gram(BEngine& E, cudaStream_t st) {
 
 template <int EPL>
 static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t st) {
-    static bool attr_set = false;
-    static bool p2p = false;
-    static int mixed = 0;
-    const int smem = (int)sizeof(EigSmem<EPL>);
-    if (!attr_set) {
-        p2p = getenv("MUSED_EIG_P2P") && atoi(getenv("MUSED_EIG_P2P")) != 0;
-        mixed = getenv("MUSED_EIG_MIXED") ? atoi(getenv("MUSED_EIG_MIXED")) : 1;   // 0 = float64 sweeps only
-        MUSED_CUDA(cudaFuncSetAttribute(k_eig_jacobi<EPL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        MUSED_CUDA(cudaFuncSetAttribute(k_eig_jacobi<EPL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr_set = true;
-    }
+    static const int mixed = getenv("MUSED_EIG_MIXED") ? atoi(getenv("MUSED_EIG_MIXED")) : 1;   // 0 = float64 sweeps only
+    const int smem = (int)ESLayout<EPL>::BYTES;
+    MUSED_SMEM_ATTR(k_eig_jacobi<EPL>, smem);
     EigArgs A;
     A.slots = E.D.slots;
     A.G = E.D.G;
@@ -481,7 +470,7 @@ static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t 
     A.Gs = E.D.Gs;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(E.D.S * EPL));
-    cfg.blockDim = dim3(EIG_NT);
+    cfg.blockDim = dim3(ES_NT);
     cfg.dynamicSmemBytes = (size_t)smem;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -491,8 +480,7 @@ static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t 
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    if (p2p) MUSED_CUDA(cudaLaunchKernelEx(&cfg, k_eig_jacobi<EPL, true>, A));
-    else MUSED_CUDA(cudaLaunchKernelEx(&cfg, k_eig_jacobi<EPL, false>, A));
+    MUSED_CUDA(cudaLaunchKernelEx(&cfg, k_eig_jacobi<EPL>, A));
     return 0;
 }
 
@@ -543,11 +531,7 @@ int bengine_chunk_finish(BEngine* Ep, cudaStream_t st) {
         if (rc) return rc;
         E.mark(3, st);
         E.mark(4, st);
-        static bool rot_attr = false;
-        if (!rot_attr) {
-            MUSED_CUDA(cudaFuncSetAttribute(k_rotate_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, RotCfg::SMEM_BYTES));
-            rot_attr = true;
-        }
+        MUSED_SMEM_ATTR(k_rotate_tc, RotCfg::SMEM_BYTES);
         k_rotate_tc<<<dim3((unsigned)((D.d + RotCfg::NT - 1) / RotCfg::NT), (unsigned)D.S), 192, RotCfg::SMEM_BYTES, st>>>(
             E.tr_t_hi, E.tr_t_lo, E.tr_sk_hi, E.tr_sk_lo, E.tr_x_hi, E.tr_x_lo, D);
         MUSED_CUDA(cudaGetLastError());

@@ -2,7 +2,7 @@
 // (swfd_engine.cu) forwards to.
 #pragma once
 #include "common.cuh"
-#include "eig_jacobi.cuh"
+#include "eig_common.cuh"
 
 namespace mused {
 

@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <string>
+#include <atomic>
 
 #include "../../include/mused_b200.h"
 
@@ -29,6 +30,19 @@ void set_error(const char* fmt, ...);
             mused::set_error(__VA_ARGS__);  \
             return MUSED_ERR_ARG;           \
         }                                   \
+    } while (0)
+
+// Opt a kernel in to more than 48 KB of dynamic shared memory, once per DEVICE (the attribute belongs to the
+// device's context; a process may drive several GPUs and several host threads).
+#define MUSED_SMEM_ATTR(func, bytes)                                                                       \
+    do {                                                                                                   \
+        static std::atomic<unsigned long long> _done{0ull};                                                \
+        int _dev = 0;                                                                                      \
+        MUSED_CUDA(cudaGetDevice(&_dev));                                                                  \
+        if (!((_done.load(std::memory_order_acquire) >> (_dev & 63)) & 1ull)) {                            \
+            MUSED_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+            _done.fetch_or(1ull << (_dev & 63), std::memory_order_release);                                \
+        }                                                                                                  \
     } while (0)
 
 __device__ __forceinline__ double warp_sum(double v) {

@@ -66,7 +66,7 @@ __device__ __forceinline__ bool flag_wait(const unsigned long long* f, unsigned 
 
 // Rotation of the column pair with inner product g and squared norms (nx, ny):
 // x' = c x - s y, y' = s x + c y.  20-bit seeds for the tangent, (c, s) refined to
-// c^2 + s^2 = 1 in float64 (same scheme as eig_jacobi.cuh).
+// c^2 + s^2 = 1 in float64 (same scheme as eig_smem.cuh).
 __device__ __forceinline__ void angle(double g, double nx, double ny, double nmax, double& off, double& c,
                                       double& s) {
     const double prod = nx * ny;

@@ -18,7 +18,7 @@
 // views of the SAME shared-memory tile.
 #pragma once
 #include "umma.cuh"
-#include "eig_jacobi.cuh"
+#include "eig_common.cuh"
 
 namespace mused {
 

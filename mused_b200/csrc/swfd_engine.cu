@@ -336,11 +336,7 @@ static int launch_eig_big(const QueryScratch& Q, int n, int sm_count, cudaStream
     if (smem > 227u * 1024u || P > sm_count || P > 256 || nr > Q.ldt || 2 * P * CB > Q.npad_max ||
         (size_t)P * CB * nr > Q.mail_count)
         return 0;
-    static bool attr_done = false;
-    if (!attr_done) {
-        MUSED_CUDA(cudaFuncSetAttribute(big::k_eig_big<CB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_done = true;
-    }
+    MUSED_SMEM_ATTR(big::k_eig_big<CB>, 227 * 1024);
     int nb = 0;
     MUSED_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, big::k_eig_big<CB>, big::NT, smem));
     if (nb < 1) return 0;
