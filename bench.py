@@ -10,9 +10,13 @@ cosine+threshold+argmax assignment of the window's rows against 150 centroids.
   python bench.py [--gpus N] [--steps K] [--warmup W]          # B200 arm
   python bench.py --impl reference ...                          # CPU arm (oracle port)
 
-N > 1 (torchrun): every rank runs an independent stream (the path shards by
-independent streams/windows; no data-path collective), value = rows of all
-ranks / max-over-ranks time, scaling "weak".
+N > 1 (torchrun): `value` = every rank runs an independent stream (the path shards by
+independent streams/windows; no data-path collective), rows of all ranks / max-over-ranks
+time, scaling "weak" -- the same metric and config as N = 1.  The line also carries
+`sharded`: north_star's column-sharded mode (d split over the N ranks, one NCCL allreduce of
+the Gram per shrink, issued from inside the C ABI on the engine's stream) on d = 16384,
+l = 128, the same stream on every rank, "scaling": "strong"; at N = 1 the same key holds the
+unsharded single-GPU figure of that shape.
 """
 from __future__ import annotations
 
@@ -46,7 +50,9 @@ def parse():
     ap.add_argument("--cpu-rows", type=int, default=0, help="rows of the cpu_baseline sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--streams", type=int, default=4, help="independent streams batched on the GPU in the multi_stream leg (0 = skip)")
+    ap.add_argument("--streams", default="4,16", help="comma list: independent streams batched per GPU by the native "
+                    "many-streams engine in the multi_stream leg ('' = skip)")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the column-sharded d=16384 leg")
     ap.add_argument("--phase-times", action="store_true", help="diagnostic: synchronise after assign and print fit/get/assign wall ms")
     ap.add_argument("--schedule", default="batched", choices=["batched", "reference"],
                     help="batched: north_star's chunked tensor-core schedule (headline); "
@@ -163,6 +169,43 @@ def cpu_port_rate(A, R, C, warm_rows, rows, with_query=True):
     return rows / dt, dt
 
 
+def blas_limit(n):
+    from threadpoolctl import threadpool_limits
+    return threadpool_limits(limits=n, user_api="blas")
+
+
+def calibrate_blas_threads(A, R, rows=16):
+    """The port's hot call is a LAPACK gesvd of a (l + b) x d buffer, b small: OpenBLAS threads can hurt (round 1:
+    16 threads 13.3 rows/s, 1 thread 21.6 rows/s).  Time `rows` rows with 1 thread and with all, keep the faster."""
+    from oracle import swfd_oracle as so
+    best = (None, 0.0)
+    A64 = A[:64 + 2 * rows].astype(np.float64)
+    for n in (1, os.cpu_count() or 1):
+        with blas_limit(n):
+            sk = so.SeqSWFD(WIN, R, D, ELL)
+            for t in range(64):
+                sk.fit(A64[t:t + 1])
+            t0 = time.perf_counter()
+            for t in range(64, 64 + rows):
+                sk.fit(A64[t:t + 1])
+            rate = rows / (time.perf_counter() - t0)
+        if rate > best[1]:
+            best = (n, rate)
+    return best[0]
+
+
+def cpu_batched_rate(A, R, rows):
+    """rows/s of oracle/swfd_batched_oracle.py (the float64 statement of the batched schedule) on the host."""
+    from oracle.swfd_batched_oracle import BatchedSeqSWFD
+    sk = BatchedSeqSWFD(WIN, R, D, ELL)
+    A64 = A[:ELL + rows].astype(np.float64)
+    sk.fit(A64[:ELL])
+    t0 = time.perf_counter()
+    sk.fit(A64[ELL:ELL + rows])
+    dt = time.perf_counter() - t0
+    return rows / dt, dt
+
+
 def host_threads():
     try:
         from threadpoolctl import threadpool_info
@@ -183,6 +226,9 @@ def run_reference(args, rank, world):
     A, R = make_stream(max(total, 2048), seed=0)
     C = centroids(0)
     from oracle import swfd_oracle as so, ops_oracle
+    nthr = calibrate_blas_threads(A, R)
+    ctx = blas_limit(nthr)
+    ctx.__enter__()
     sk = so.SeqSWFD(WIN, R, D, ELL)
     A64 = A[:total].astype(np.float64)
     for t in range(warm_fill):
@@ -203,7 +249,8 @@ def run_reference(args, rank, world):
     # one get() per window of WIN rows, amortised like the B200 arm does
     sec_per_row = sum(timed) / (len(timed) * rows_per_step) + tq / WIN
     value = 1.0 / sec_per_row
-    cores = host_threads()
+    ctx.__exit__(None, None, None)
+    cores = nthr
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(timed) / len(timed),
@@ -212,8 +259,10 @@ def run_reference(args, rank, world):
         "config": {"workload": "SWFD d=1024 l=128 N=10000 low-rank+noise stream + cosine assign k=150 (configs[1])",
                    "schedule": "reference", "levels": sk.logR},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": "%d timed steps of %d rows after %d warm-up rows; one get() of %.3fs amortised over %d rows"
-                                   % (args.steps, rows_per_step, warm_fill + args.warmup * rows_per_step, tq, WIN)},
+                         "sample": "%d timed steps of %d rows after %d warm-up rows; one get() of %.3fs amortised over %d rows; "
+                                   "BLAS threads = %d (the faster of 1 and %d on a 16-row calibration)"
+                                   % (args.steps, rows_per_step, warm_fill + args.warmup * rows_per_step, tq, WIN,
+                                      nthr, os.cpu_count() or 1)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -315,43 +364,59 @@ def run_ours(args, rank, local_rank, world):
     main_res = device_arm(args.schedule, args.warmup, args.steps, True)
     other = None
     if args.schedule == "batched" and not args.no_refsched:
-        # the bit-faithful reference flush schedule on the same stream (1 warm-up + 2 timed windows)
+        # the bit-faithful reference flush schedule on the same stream (1 warm-up + 2 timed windows), device-resident
+        # rows, then one more window from HOST buffers through the same public calls (its e2e)
         other = device_arm("reference", 1, min(2, args.steps), False)
+        sk3 = SeqBasedSWFD(WIN, R, D, ELL, device=local_rank, cluster=args.cluster, schedule="reference")
+        sk3.fit(A[:WIN])
+        sk3.get()
+        lab_h = torch.empty(WIN, dtype=torch.int32).pin_memory()
+        barrier()
+        e0.record()
+        sk3.fit(A[WIN:2 * WIN])                        # numpy host rows: H2D inside the C-ABI call
+        sk3.get()
+        lab_h.copy_(mo.cosine_assign(torch.as_tensor(A[WIN:2 * WIN]).to(dev), Cd, TAU, device=dev))
+        e1.record()
+        barrier()
+        other["e2e_value"] = world * WIN / (max_over_ranks(e0.elapsed_time(e1)) * 1e-3)
+        sk3.close()
 
-    # ---------------- independent streams batched on one GPU (north_star: "independent streams and
-    # windows are batched per GPU"): K sketches, each on its own CUDA stream, same step per stream
+    # ---------------- independent streams batched on one GPU (north_star: "independent streams and windows are
+    # batched per GPU"; configs[4]: "64 independent windows batched per GPU"): the native many-streams engine
+    # (mused_swfd_cfg.n_streams): ONE K1..K5 launch sequence per chunk covers K x 2 x levels FD instances
     multi = None
-    if args.schedule == "batched" and args.streams > 1 and n_steps >= 2:
-        K, wins = args.streams, min(2, n_steps - 1)
-        engines = [SeqBasedSWFD(WIN, R, D, ELL, device=local_rank, schedule="batched") for _ in range(K)]
-        streams = [torch.cuda.Stream(device=dev) for _ in range(K)]
-        blkrows = 10 * ELL
-
-        def feed(w):
-            for off in range(0, WIN, blkrows):                        # interleave the streams block by block
-                for k in range(K):
-                    lo = ((w + k) % n_steps) * WIN + off              # every sketch reads its own windows
-                    with torch.cuda.stream(streams[k]):
-                        engines[k].fit(Ad[lo:lo + min(blkrows, WIN - off)])
+    ks = [int(x) for x in str(args.streams).split(",") if x.strip()] if args.schedule == "batched" else []
+    if ks and n_steps >= 3:
+        from mused_b200.swfd import MultiStreamSWFD
+        multi = {"unit": UNIT, "api": "MultiStreamSWFD / mused_swfd_fit_streams (n_streams handles, one launch sequence)",
+                 "step": "fit of one window per stream + get() of every stream + assign of every stream's window",
+                 "by_streams": {}}
+        for K in ks:
+            wins = 2
+            # K x rows x d, resident before timing; streams cycle through this rank's windows at different offsets
+            Ak = torch.stack([Ad[((k % n_steps) * WIN):((k % n_steps) * WIN) + WIN] for k in range(K)])
+            Aw = [torch.stack([Ad[(((k + w) % n_steps) * WIN):(((k + w) % n_steps) * WIN) + WIN] for k in range(K)])
+                  for w in range(1, 1 + wins)]
+            msk = MultiStreamSWFD(K, WIN, R, D, ELL, device=local_rank)
+            msk.fit(Ak)
             for k in range(K):
-                wk = (w + k) % n_steps
-                with torch.cuda.stream(streams[k]):
-                    engines[k].get()
-                    mo.cosine_assign(Ad[wk * WIN:(wk + 1) * WIN], Cd, TAU, device=dev)
-
-        feed(0)
-        barrier()
-        t0 = time.perf_counter()
-        for w in range(1, 1 + wins):
-            feed(w)
-        barrier()
-        dt = max_over_ranks(time.perf_counter() - t0)
-        multi = {"streams_per_gpu": K, "value": world * K * wins * WIN / dt, "unit": UNIT,
-                 "note": "aggregate over %d independent sketches per GPU, one CUDA stream each, same step "
-                         "(fit + get + assign per window); the single-stream eigensolve leaves most issue "
-                         "slots idle, independent streams fill them" % K}
-        for e in engines:
-            e.close()
+                msk.get(k)
+            barrier()
+            e0.record()
+            for w in range(wins):
+                msk.fit(Aw[w])
+                for k in range(K):
+                    msk.get(k)
+                mo.cosine_assign(Aw[w].reshape(K * WIN, D), Cd, TAU, device=dev)
+            e1.record()
+            barrier()
+            ms = max_over_ranks(e0.elapsed_time(e1))
+            multi["by_streams"][str(K)] = {"value": world * K * wins * WIN / (ms * 1e-3), "ms_per_window": ms / wins}
+            msk.close()
+            del Ak, Aw, msk
+            torch.cuda.empty_cache()
+        best = max(multi["by_streams"].items(), key=lambda kv: kv[1]["value"])
+        multi["streams_per_gpu"], multi["value"] = int(best[0]), best[1]["value"]
 
     # ---------------- end-to-end arm (`e2e`): host buffers through the public API
     e2e = None
@@ -411,24 +476,28 @@ def run_ours(args, rank, local_rank, world):
         dom = max(km, key=km.get)
         dur_s = km[dom] / chunks * 1e-3
         achieved = bytes_per_row * rows_per_launch / dur_s / 1e9
-        # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full of this workload
-        # (profiles/r01_ncu_full_summary.csv, K3: profiles/r01_ncu_k3_mixed_stalls.csv); the FD state is L2-resident,
-        # hence far below the algorithmic bytes
-        ncu_traffic = {"K3_eig": 6481920, "K2_gram": 13872640 + 1511680, "K1_stage": 33566976 + 11879680,
-                       "K5_book": 127232, "K4_rotate": 16892416 + 84224}
-        roofline = {"bound": "hbm", "kernel": {"K1_stage": "k_bstage", "K5_book": "k_bbook", "K2_gram": "k_gram_tc",
-                                                "K3_eig": "k_eig_jacobi", "K4_rotate": "k_rotate_tc"}[dom],
+        # dram bytes / issue figures of the dominant kernel come from the committed ncu capture of THIS command
+        # (profiles/r02_ncu_dominant.json, written by tools/ncu_summarise.py); absent -> null, never a pasted constant
+        ncu = {}
+        pj = os.path.join(ROOT, "profiles", "r02_ncu_dominant.json")
+        if os.path.exists(pj):
+            with open(pj) as f:
+                ncu = json.load(f)
+        kname = {"K1_stage": "k_bstage", "K5_book": "k_bbook", "K2_gram": "k_gram_tc",
+                 "K3_eig": "k_eig_jacobi", "K4_rotate": "k_rotate_tc"}[dom]
+        nk = ncu.get(kname, {})
+        roofline = {"bound": "hbm", "kernel": kname,
                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": ncu_traffic.get(dom),
-                    "issue_active_pct": 23.6 if dom == "K3_eig" else None,
-                    "cycles_per_issued_instruction": 4.23 if dom == "K3_eig" else None,
+                    "traffic": nk.get("dram_bytes_per_launch"),
+                    "ncu": {k: v for k, v in nk.items() if k != "dram_bytes_per_launch"} or None,
                     "peak_source": how, "algorithmic_bytes_per_row": bytes_per_row,
                     "rows_per_launch": rows_per_launch, "avg_launch_ms": km[dom] / chunks,
                     "share_of_step": km[dom] / main_res["ms_total"],
-                    "note": "dominant kernel is the batched mixed-precision Jacobi eigensolve: one warp per scheduler, "
-                            "4.2 cycles per issued instruction (dependency wait 1.5, shuffle/MUFU scoreboard 0.65, "
-                            "cluster barrier + fence 0.64, DSMEM 0.19, instruction fetch 0.16) -- a dependent-issue chain, no HBM or tensor roofline applies; "
-                            "bytes are SURVEY 8(d)'s per-row figure"}
+                    "note": "dominant kernel is the batched mixed-precision Jacobi eigensolve (shared-memory resident, 8 warps "
+                            "x 2-column register blocks per CTA, cluster of 8 CTAs per FD instance): a sweep is 255 dependent "
+                            "rotation steps of ~600 cycles each (dot -> 5 shuffle stages -> angle with 2 MUFU -> broadcast -> "
+                            "rotate), ~10 sweeps per chunk -- a dependent-issue chain, no HBM or tensor roofline applies; "
+                            "bytes are SURVEY 8(d)'s per-row figure (DESIGN.md section 4, cycle accounting in profiles/)"}
         n2 = 2 * ELL
         us = {k: v / chunks * 1e3 for k, v in km.items()}
         kernels = {
@@ -461,22 +530,54 @@ def run_ours(args, rank, local_rank, world):
                     "share_of_step": main_res["k_ms"] / main_res["ms_total"],
                     "note": "reference flush schedule is a per-row dependency chain (latency/FP64-bound), see DESIGN.md"}
 
-    # covariance error of the last timed window, both schedules, against the exact window
+    # covariance error ON ONE WINDOW for all three: rows 0..10000 of the fixture stream of tests/golden/full_c1.npz
+    # (generated offline by the UNMODIFIED reference, oracle/gen_golden_full.py), queries at the fixture's times
     from oracle import swfd_oracle as so
-    Aw = A[(n_steps - 1) * WIN:n_steps * WIN].astype(np.float64)
-    cov = {args.schedule: so.cov_error(Aw, main_res["sketch"]), "bound_1_over_l": 1.0 / ELL}
-    if other is not None:
-        lastw = 1 + min(2, args.steps)
-        cov["reference_schedule_window"] = so.cov_error(A[(lastw - 1) * WIN:lastw * WIN].astype(np.float64),
-                                                        other["sketch"])
+    cov = {"bound_1_over_l": 1.0 / ELL,
+           "last_timed_window_" + args.schedule: so.cov_error(A[(n_steps - 1) * WIN:n_steps * WIN].astype(np.float64),
+                                                               main_res["sketch"])}
+    fx = os.path.join(ROOT, "tests", "golden", "full_c1.npz")
+    if os.path.exists(fx):
+        import hashlib
+        from mused_b200 import synth
+        g = np.load(fx)
+        Af = synth.lowrank_stream(int(g["n"]), D, seed=0)
+        if hashlib.sha256(np.ascontiguousarray(Af).tobytes()).hexdigest() == str(g["sha_A"]):
+            qts = [int(t) for t in g["q_t"] if int(t) <= WIN]
+            Afd = torch.as_tensor(Af).to(dev)
+            errs = {}
+            for sched in ("reference", "batched"):
+                skf = SeqBasedSWFD(WIN, R, D, ELL, device=local_rank, schedule=sched)
+                t0_ = 0
+                for t in qts:
+                    skf.fit(Afd[t0_:t])
+                    t0_ = t
+                    Bf = skf.get()[0]
+                errs[sched] = so.cov_error(Af[max(0, qts[-1] - WIN):qts[-1]].astype(np.float64), Bf)
+                skf.close()
+            qi = list(g["q_t"]).index(qts[-1])
+            cov.update({"window": "rows %d..%d of the fixture stream (tests/golden/full_c1.npz), queries at %s"
+                                  % (max(0, qts[-1] - WIN), qts[-1], qts),
+                        "reference_cpu": float(g["cov_err"][qi]),
+                        "reference_cpu_source": "imported reference, generated offline (%s)" % str(g["versions"]),
+                        "reference_schedule_gpu": errs["reference"], "batched_gpu": errs["batched"],
+                        "rel_diff_reference_schedule": abs(errs["reference"] - float(g["cov_err"][qi])) / float(g["cov_err"][qi])})
+        else:
+            cov["window"] = "fixture stream mismatch: same-window comparison skipped"
 
-    cpu = None
+    cpu, cpu_b = None, None
     if not args.no_cpu:
-        rows = args.cpu_rows or 256
-        v, dt = cpu_port_rate(A, R, Cn, warm_rows=256, rows=rows)
-        cpu = {"value": v, "unit": UNIT, "cores": host_threads(), "kind": "port",
-               "sample": "rows 256..%d of the same stream (after 256 untimed warm-up rows) + one get() + assign, %.1fs"
-                         % (256 + rows, dt)}
+        rows = args.cpu_rows or 384
+        nthr = calibrate_blas_threads(A, R)
+        with blas_limit(nthr):
+            v, dt = cpu_port_rate(A, R, Cn, warm_rows=384, rows=rows)
+            vb, dtb = cpu_batched_rate(A, R, rows=8 * ELL)
+        cpu = {"value": v, "unit": UNIT, "cores": nthr, "kind": "port",
+               "sample": "rows 384..%d of the same stream (after 384 untimed warm-up rows) + one get() + assign, %.1fs; "
+                         "BLAS threads = %d (the faster of 1 and %d on a 16-row calibration)"
+                         % (384 + rows, dt, nthr, os.cpu_count() or 1)}
+        cpu_b = {"value": vb, "unit": UNIT, "cores": nthr, "kind": "port (oracle/swfd_batched_oracle.py, the float64 "
+                 "statement of the batched schedule)", "sample": "%d rows after %d warm-up rows, %.1fs" % (8 * ELL, ELL, dtb)}
 
     st = main_res["state"]
     line = {
@@ -490,6 +591,7 @@ def run_ours(args, rank, local_rank, world):
                          "FD state is meant to stay L2-resident",
                    "query_level": main_res["level"]},
         "clocks": main_res["clocks"], "multi_stream": multi, "get_ms_per_step": main_res["get_ms"],
+        "cpu_batched_baseline": cpu_b,
         "fit_ms_per_step": main_res["fit_ms"], "assign_ms_per_step": main_res["assign_ms"] if args.phase_times else None, "e2e": e2e, "gpu_launches": main_res["launches"], "roofline": roofline,
         "cpu_baseline": cpu, "cov_error": cov,
         "flushes_per_row": sum(o["n_flush"] for o in st) / float(n_steps * WIN),
@@ -498,9 +600,19 @@ def run_ours(args, rank, local_rank, world):
         line["kernels"] = kernels
     if other is not None:
         line["reference_schedule"] = {"value": other["value"], "unit": UNIT, "dtype": "f64",
+                                      "e2e_value": other.get("e2e_value"),
                                       "ms_per_step": other["ms_total"] / min(2, args.steps),
+                                      "k_swfd_rows_share_of_step": (other["k_ms"] / other["ms_total"]) if other.get("k_ms") else None,
                                       "note": "bit-faithful flush/dump schedule of the reference on the same stream "
                                               "(strict parity path, tests/test_swfd_gpu.py)"}
+    if cpu and cpu_b:
+        # like-for-like ratios (same schedule on both sides); the driver computes its own from the two arms
+        line["speedup_same_schedule"] = {
+            "strict": (other["value"] / world / cpu["value"]) if other is not None else None,
+            "strict_e2e": (other["e2e_value"] / world / cpu["value"]) if other is not None and other.get("e2e_value") else None,
+            "batched": main_res["value"] / world / cpu_b["value"],
+            "note": "per-GPU rows/s of a schedule / CPU rows/s of the SAME schedule (strict: reference flush schedule vs "
+                    "oracle/swfd_oracle.py; batched: vs oracle/swfd_batched_oracle.py)"}
     if args.schedule == "reference":
         ph_tot = {}
         for p in main_res["prof"]:

@@ -69,6 +69,9 @@ typedef struct {
     int64_t chunk_rows;       /* rows staged per launch; 0 = auto                        */
     int32_t schedule;         /* MUSED_SCHEDULE_REFERENCE | MUSED_SCHEDULE_BATCHED       */
     int32_t batch_rows;       /* batched: rows per shrink (<= ell); 0 = ell              */
+    int32_t n_streams;        /* batched: independent streams advanced in lock-step by one
+                                 launch sequence (north_star: "independent streams and windows
+                                 are batched per GPU"); 0 / 1 = one stream                  */
 } mused_swfd_cfg;
 
 /* REFERENCE: every flush / dump decision of the reference, row by row
@@ -91,6 +94,20 @@ int mused_swfd_destroy(mused_swfd_t* h);
  * when the call returns (host) / when `stream` reaches this point (device). */
 int mused_swfd_fit(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld,
                    int dtype, int where, void* stream);
+
+/* n_streams independent sketches behind one handle (cfg.n_streams = K, schedule = BATCHED): every stream
+ * follows SeqBasedSWFD semantics (seq_based_swfd.py:11-103) on its own rows and shares nothing with the
+ * others; one K1..K5 launch sequence per chunk covers the K x 2 x levels FD instances.  fit_streams feeds
+ * n_rows rows to EVERY stream: stream k's rows start at rows + k * stream_stride elements (row-major, ld).
+ * get_stream / size_stream / debug_stream address stream k (get closes the open chunk of all streams,
+ * as SeqBasedSWFD.get flushes, then reads stream k without further mutation). */
+int mused_swfd_fit_streams(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld, int64_t stream_stride,
+                           int dtype, int where, void* stream);
+int mused_swfd_get_stream(mused_swfd_t* h, int32_t k, double* sketch, double* sigma2, double* vt, double* delta,
+                          int32_t* level, int where, void* stream);
+int mused_swfd_size_stream(mused_swfd_t* h, int32_t k, int64_t* n);
+int mused_swfd_debug_stream(mused_swfd_t* h, int32_t k, double* scal, double* sigma2, uint64_t* q_s, uint64_t* q_t,
+                            int64_t q_cap);
 
 /* TimeBasedSWFD.fit(X, t) (swfd/seq_based_swfd.py:150-189): the same per-row rules with an
  * explicit arrival time per row instead of the running counter; times[r] (HOST array of n_rows

@@ -26,7 +26,7 @@ class SwfdCfg(C.Structure):
     _fields_ = [("N", C.c_int64), ("d", C.c_int64), ("ell", C.c_int64), ("beta", C.c_double),
                 ("n_levels", C.c_int32), ("thresholds", C.POINTER(C.c_double)),
                 ("device", C.c_int32), ("cluster", C.c_int32), ("chunk_rows", C.c_int64),
-                ("schedule", C.c_int32), ("batch_rows", C.c_int32)]
+                ("schedule", C.c_int32), ("batch_rows", C.c_int32), ("n_streams", C.c_int32)]
 
 
 SCHEDULES = {"reference": 0, "batched": 1}
@@ -46,6 +46,7 @@ SYMBOLS = [
     "mused_fd_dump", "mused_fd_flush", "mused_fd_get",
     "mused_assign", "mused_topk_adjacency", "mused_contingency", "mused_sym_eig",
     "mused_topk_adjacency_f64", "mused_swfd_kernel_gaps", "mused_swfd_fit_timed",
+    "mused_swfd_fit_streams", "mused_swfd_get_stream", "mused_swfd_size_stream", "mused_swfd_debug_stream",
 ]
 
 
@@ -80,6 +81,10 @@ def load():
     lib.mused_swfd_fit.argtypes = [vp, vp, i64, i64, C.c_int, C.c_int, vp]
     lib.mused_swfd_fit_timed.argtypes = [vp, vp, i64, i64, C.c_int, C.c_int, vp, vp]
     lib.mused_swfd_get.argtypes = [vp, vp, vp, vp, C.POINTER(dbl), C.POINTER(i32), C.c_int, vp]
+    lib.mused_swfd_fit_streams.argtypes = [vp, vp, i64, i64, i64, C.c_int, C.c_int, vp]
+    lib.mused_swfd_get_stream.argtypes = [vp, i32, vp, vp, vp, C.POINTER(dbl), C.POINTER(i32), C.c_int, vp]
+    lib.mused_swfd_size_stream.argtypes = [vp, i32, C.POINTER(i64)]
+    lib.mused_swfd_debug_stream.argtypes = [vp, i32, vp, vp, vp, vp, i64]
     lib.mused_swfd_size.argtypes = [vp, C.POINTER(i64)]
     lib.mused_swfd_time.argtypes = [vp, C.POINTER(C.c_uint64)]
     lib.mused_swfd_debug.argtypes = [vp, vp, vp, vp, vp, i64]

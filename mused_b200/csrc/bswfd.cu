@@ -25,11 +25,14 @@ namespace mused {
 // reduction order for ||x||^2 (it decides routing, seq_based_swfd.py:76-77).
 // ---------------------------------------------------------------------------
 template <class Tin>
-__global__ void __launch_bounds__(256) k_bstage(const Tin* __restrict__ in, long long ld, long long d_in, long long d,
+__global__ void __launch_bounds__(256) k_bstage(const Tin* __restrict__ in, long long ld, long long stream_stride,
+                                                long long xrows, long long d_in, long long d,
                                                 int row_off, float* __restrict__ xhi,
                                                 float* __restrict__ xlo, double* __restrict__ norm2) {
     __shared__ double red[8];
     const int r = blockIdx.x;
+    in += (size_t)blockIdx.y * stream_stride;                 // grid.y = stream
+    row_off += (int)(blockIdx.y * xrows);
     const Tin* src = in + (size_t)r * ld;
     float* hi = xhi + (size_t)(row_off + r) * d;
     float* lo = xlo + (size_t)(row_off + r) * d;
@@ -56,10 +59,13 @@ __global__ void __launch_bounds__(256) k_bstage(const Tin* __restrict__ in, long
 // (the append is pure streaming: 4 bytes read and 8 written per element).  Same contract as
 // k_bstage: hi / lo planes and ||x||^2 in a fixed order (lane partials in element order, then the
 // xor tree) that does not depend on how the caller slices the stream.
-__global__ void __launch_bounds__(256) k_bstage_v4(const float* __restrict__ in, long long ld, long long d_in, long long d, long long m,
+__global__ void __launch_bounds__(256) k_bstage_v4(const float* __restrict__ in, long long ld, long long stream_stride,
+                                                   long long xrows, long long d_in, long long d, long long m,
                                                    int row_off, float* __restrict__ xhi, float* __restrict__ xlo,
                                                    double* __restrict__ norm2) {
     const int lane = threadIdx.x & 31;
+    in += (size_t)blockIdx.y * stream_stride;                 // grid.y = stream
+    row_off += (int)(blockIdx.y * xrows);
     const long long warps = (long long)gridDim.x * 8;
     for (long long r = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); r < m; r += warps) {
         const float4* src = reinterpret_cast<const float4*>(in + (size_t)r * ld);
@@ -98,7 +104,8 @@ __global__ void __launch_bounds__(256) k_bbook(BDev D, int n, unsigned long long
     unsigned long long* qs = D.ringS + (size_t)s * D.capn;
     unsigned long long* qt = D.ringT + (size_t)s * D.capn;
     // routing test of every row in parallel (seq_based_swfd.py:76-77); the serial part below only walks flags
-    for (int r = threadIdx.x; r < n; r += 256) is_raw[r] = D.norm2[D.x0 + r] >= sl.error ? 1 : 0;
+    const double* nrm2 = D.norm2 + (size_t)(s / D.S1) * D.xrows + D.x0;
+    for (int r = threadIdx.x; r < n; r += 256) is_raw[r] = nrm2[r] >= sl.error ? 1 : 0;
     __syncthreads();
     if (threadIdx.x == 0) {
         int reset = 0;
@@ -226,19 +233,22 @@ __global__ void k_bfd_out(BDev D, int s, double* sketch, double* sigma2, double*
 struct BEngine {
     BDev D{};
     int device = 0, n_levels = 0, sm_count = 148;
+    int K = 1;                        // independent streams advanced in lock-step (same rows per fit() call each)
     long long batch = 0;
     unsigned long long time = 0;      // rows handed to fit()
     unsigned long long done = 0;      // rows folded into the state
     int pend = 0;                     // rows staged in the chunk planes, not yet processed
     CUtensorMap tm_sk_hi, tm_sk_lo, tm_x_hi, tm_x_lo;                 // K2 boxes: l rows x 32 columns
     CUtensorMap tr_t_hi, tr_t_lo, tr_sk_hi, tr_sk_lo, tr_x_hi, tr_x_lo; // K4 boxes
-    unsigned char* raw = nullptr;     // H2D staging of caller rows
+    unsigned char* raw = nullptr;     // H2D staging of caller rows: [K][raw_rows][d] of the widest dtype
     size_t raw_bytes = 0;
+    long long raw_rows = 0;
     long long sb_rows = 0;            // rows of the staging planes (+ ell of slack for the last TMA box)
     long long ahead = 0;              // rows staged beyond the open chunk (inside one fit() call)
     QueryScratch Q;
     double *o_sketch = nullptr, *o_vt = nullptr, *o_s2 = nullptr, *o_delta = nullptr;
     std::vector<void*> allocs;
+    cudaStream_t last_stream = nullptr;   // stream of the last fit(): size / debug read the slots behind it
     int q_slot = 0, q_ng = 0;         // pending query (get_begin -> get_finish)
     bool q_gram = true;               // get_begin left the stack Gram in Q.G
     bool timing = false;
@@ -288,7 +298,7 @@ static size_t b_dtype_size(int dt) {
 }
 
 int bengine_create(BEngine** out, long long N, long long d, long long ell, double beta, int n_levels,
-                   const double* thr, int device, long long batch) {
+                   const double* thr, int device, long long batch, int n_streams) {
     int ndev = 0;
     cudaError_t ce = cudaGetDeviceCount(&ndev);
     if (ce != cudaSuccess || ndev == 0) {
@@ -307,19 +317,24 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     d = (d_l + 31) / 32 * 32;
     MUSED_REQUIRE(N >= 1 && beta > 0, "bad N / beta");
     MUSED_REQUIRE(n_levels >= 0 && n_levels <= 64, "n_levels out of range");
+    MUSED_REQUIRE(n_streams >= 1 && n_streams <= 1024 && (long long)n_streams * 2 * n_levels <= 65535,
+                  "n_streams out of range (1 .. 1024, n_streams * 2 * levels <= 65535)");
     if (batch <= 0) batch = ell_l;
     MUSED_REQUIRE(batch <= ell_l, "batch_rows must be <= sketch_dim");
     MUSED_CUDA(cudaSetDevice(device));
     BEngine* E = new BEngine();
     E->device = device;
     E->n_levels = n_levels;
+    E->K = n_streams;
     E->batch = batch;
     cudaDeviceProp prop;
     MUSED_CUDA(cudaGetDeviceProperties(&prop, device));
     E->sm_count = prop.multiProcessorCount;
     BDev& D = E->D;
-    const int S = 2 * n_levels;
+    const int S1 = 2 * n_levels;
+    const int S = S1 * n_streams;
     D.S = S;
+    D.S1 = std::max(S1, 1);
     D.ell = (int)ell;
     D.ell_l = (int)ell_l;
     D.n2 = 2 * (int)ell;
@@ -330,7 +345,8 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     D.capn = (int)floor(D.qcap) + (int)batch + (int)ell + 2;
     // split-K: enough CTAs to cover the SMs, K slices of whole 32-float blocks
     int KS = 16;
-    while (KS > 1 && (d % (32 * KS) != 0 || (long long)S * KS > 1LL * E->sm_count)) KS >>= 1;
+    // (sized on ONE stream's instances so that a stream's arithmetic does not depend on how many share the handle)
+    while (KS > 1 && (d % (32 * KS) != 0 || (long long)S1 * KS > 1LL * E->sm_count)) KS >>= 1;
     if (getenv("MUSED_GRAM_KS")) {
         const int want = atoi(getenv("MUSED_GRAM_KS"));
         if (want >= 1 && want <= 16 && d % (32 * want) == 0) KS = want;
@@ -342,10 +358,11 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     A_(D.slots, Sa);
     A_(D.skhi, Sa * 2 * ell * d);
     A_(D.sklo, Sa * 2 * ell * d);
-    E->sb_rows = std::max<long long>(2 * ell, std::min<long long>(8192, (64ll << 20) / (d * 8)));
-    A_(D.xhi, (size_t)(E->sb_rows + ell) * d);
-    A_(D.xlo, (size_t)(E->sb_rows + ell) * d);
-    A_(D.norm2, (size_t)(E->sb_rows + ell));
+    E->sb_rows = std::max<long long>(3 * ell, std::min<long long>(8192, (64ll << 20) / (d * 8 * n_streams)));
+    D.xrows = E->sb_rows + ell;
+    A_(D.xhi, (size_t)n_streams * D.xrows * d);
+    A_(D.xlo, (size_t)n_streams * D.xrows * d);
+    A_(D.norm2, (size_t)n_streams * D.xrows);
     D.x0 = 0;
     A_(D.mask, Sa * ell);
     A_(D.Gp, Sa * KS * D.n2 * D.n2);
@@ -359,7 +376,8 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     A_(D.ringV, Sa * D.capn * d);
     A_(D.ringS, Sa * D.capn);
     A_(D.ringT, Sa * D.capn);
-    E->raw_bytes = (size_t)std::max<long long>(ell, std::min<long long>(8192, (64ll << 20) / (d * 8))) * d * 8;
+    E->raw_rows = std::max<long long>(ell, std::min<long long>(8192, (64ll << 20) / (d * 8 * n_streams)));
+    E->raw_bytes = (size_t)n_streams * E->raw_rows * d * 8;
     A_(E->raw, E->raw_bytes);
     QueryScratch& Q = E->Q;
     Q.ng_max = D.ell + D.capn + 1;
@@ -388,16 +406,17 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     std::vector<BSlot> init(Sa);
     memset(init.data(), 0, sizeof(BSlot) * Sa);
     for (int s = 0; s < S; ++s) {
-        init[s].error = thr[s / 2];
+        init[s].error = thr[(s % S1) / 2];
         init[s].last_dump = 1;       // sliding_windows_frequent_directions.py:23
-        init[s].parity = s & 1;
+        init[s].parity = (s % S1) & 1;
         init[s].skip = 1;
     }
     MUSED_CUDA(cudaMemcpy(D.slots, init.data(), sizeof(BSlot) * Sa, cudaMemcpyHostToDevice));
     CUresult r1 = encode_tmap_f32_2d(&E->tm_sk_hi, D.skhi, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
     CUresult r2 = encode_tmap_f32_2d(&E->tm_sk_lo, D.sklo, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
-    CUresult r3 = encode_tmap_f32_2d(&E->tm_x_hi, D.xhi, (uint64_t)(E->sb_rows + ell), (uint64_t)d, (uint64_t)d, (uint32_t)ell);
-    CUresult r4 = encode_tmap_f32_2d(&E->tm_x_lo, D.xlo, (uint64_t)(E->sb_rows + ell), (uint64_t)d, (uint64_t)d, (uint32_t)ell);
+    const uint64_t xtot = (uint64_t)n_streams * (uint64_t)D.xrows;
+    CUresult r3 = encode_tmap_f32_2d(&E->tm_x_hi, D.xhi, xtot, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
+    CUresult r4 = encode_tmap_f32_2d(&E->tm_x_lo, D.xlo, xtot, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
     {
         const uint32_t trows = (uint32_t)std::min<long long>(ell, 128), brows = (uint32_t)std::min<long long>(ell, 32);
         CUresult q[6];
@@ -405,8 +424,8 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
         q[1] = encode_tmap_f32_2d(&E->tr_t_lo, D.Tlo, (uint64_t)Sa * ell, (uint64_t)D.n2, (uint64_t)D.n2, trows);
         q[2] = encode_tmap_f32_2d(&E->tr_sk_hi, D.skhi, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, brows, 32, true);
         q[3] = encode_tmap_f32_2d(&E->tr_sk_lo, D.sklo, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, brows, 32, true);
-        q[4] = encode_tmap_f32_2d(&E->tr_x_hi, D.xhi, (uint64_t)(E->sb_rows + ell), (uint64_t)d, (uint64_t)d, brows, 32, true);
-        q[5] = encode_tmap_f32_2d(&E->tr_x_lo, D.xlo, (uint64_t)(E->sb_rows + ell), (uint64_t)d, (uint64_t)d, brows, 32, true);
+        q[4] = encode_tmap_f32_2d(&E->tr_x_hi, D.xhi, xtot, (uint64_t)d, (uint64_t)d, brows, 32, true);
+        q[5] = encode_tmap_f32_2d(&E->tr_x_lo, D.xlo, xtot, (uint64_t)d, (uint64_t)d, brows, 32, true);
         for (int i = 0; i < 6; ++i)
             if (q[i] != CUDA_SUCCESS) r1 = q[i];
     }
@@ -436,6 +455,8 @@ static int launch_gram(BEngine& E, cudaStream_t st) {
     A.KS = E.D.KS;
     A.kblocks = (int)(E.D.d / (32 * E.D.KS));
     A.x0 = E.D.x0;
+    A.S1 = E.D.S1;
+    A.xrows = (int)E.D.xrows;
     k_gram_tc<N2><<<dim3(E.D.KS, E.D.S), 192, C::SMEM_BYTES, st>>>(E.tm_sk_hi, E.tm_sk_lo, E.tm_x_hi, E.tm_x_lo, A);
     MUSED_CUDA(cudaGetLastError());
     return 0;
@@ -563,26 +584,29 @@ static long long chunk_room(const BEngine& E) {
 // K1 launch: m rows behind everything already staged.  logical = the rows join the open chunk at
 // once (phase API, one chunk at a time); otherwise they wait in the planes (fit() stages a whole
 // block of caller rows with ONE launch and then walks it chunk by chunk).
-static int stage_rows(BEngine& E, const void* dev_rows, long long m, long long ld, int dtype, bool logical,
-                      cudaStream_t st) {
+static int stage_rows(BEngine& E, const void* dev_rows, long long m, long long ld, long long stream_stride, int dtype,
+                      bool logical, cudaStream_t st) {
     BDev& D = E.D;
     if (E.pend == 0 && E.ahead == 0) D.x0 = 0;
     const int row_off = D.x0 + E.pend + (int)E.ahead;
     MUSED_REQUIRE(row_off + m <= E.sb_rows + D.ell, "internal: staging planes overflow (%d + %lld rows)", row_off, m);
     E.mark(0, st);
+    const dim3 gr((unsigned)m, (unsigned)E.K);
+#define STAGE_(T) k_bstage<T><<<gr, 256, 0, st>>>((const T*)dev_rows, ld, stream_stride, D.xrows, D.d_l, D.d, row_off, D.xhi, D.xlo, D.norm2)
     switch (dtype) {
-        case MUSED_F64: k_bstage<double><<<(unsigned)m, 256, 0, st>>>((const double*)dev_rows, ld, D.d_l, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_F64: STAGE_(double); break;
         case MUSED_F32:
-            if (D.d_l % 4 == 0 && ld % 4 == 0 && ((uintptr_t)dev_rows & 15) == 0)
-                k_bstage_v4<<<(unsigned)std::min<long long>((m + 7) / 8, 16ll * E.sm_count), 256, 0, st>>>(
-                    (const float*)dev_rows, ld, D.d_l, D.d, m, row_off, D.xhi, D.xlo, D.norm2);
+            if (D.d_l % 4 == 0 && ld % 4 == 0 && stream_stride % 4 == 0 && ((uintptr_t)dev_rows & 15) == 0)
+                k_bstage_v4<<<dim3((unsigned)std::min<long long>((m + 7) / 8, std::max(1ll, 16ll * E.sm_count / E.K)), (unsigned)E.K), 256, 0, st>>>(
+                    (const float*)dev_rows, ld, stream_stride, D.xrows, D.d_l, D.d, m, row_off, D.xhi, D.xlo, D.norm2);
             else
-                k_bstage<float><<<(unsigned)m, 256, 0, st>>>((const float*)dev_rows, ld, D.d_l, D.d, row_off, D.xhi, D.xlo, D.norm2);
+                STAGE_(float);
             break;
-        case MUSED_I64: k_bstage<long long><<<(unsigned)m, 256, 0, st>>>((const long long*)dev_rows, ld, D.d_l, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
-        case MUSED_I32: k_bstage<int><<<(unsigned)m, 256, 0, st>>>((const int*)dev_rows, ld, D.d_l, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
-        case MUSED_U8: k_bstage<unsigned char><<<(unsigned)m, 256, 0, st>>>((const unsigned char*)dev_rows, ld, D.d_l, D.d, row_off, D.xhi, D.xlo, D.norm2); break;
+        case MUSED_I64: STAGE_(long long); break;
+        case MUSED_I32: STAGE_(int); break;
+        case MUSED_U8: STAGE_(unsigned char); break;
     }
+#undef STAGE_
     MUSED_CUDA(cudaGetLastError());
     E.mark(0, st);
     mused_count_launches(1);
@@ -597,39 +621,51 @@ static int compact_open_chunk(BEngine& E, cudaStream_t st) {
     BDev& D = E.D;
     if (D.x0 == 0) return 0;
     if (E.pend > 0) {
-        MUSED_REQUIRE(D.x0 >= E.pend, "internal: open chunk overlaps its destination");
-        const size_t bytes = (size_t)E.pend * D.d * sizeof(float);
-        MUSED_CUDA(cudaMemcpyAsync(D.xhi, D.xhi + (size_t)D.x0 * D.d, bytes, cudaMemcpyDeviceToDevice, st));
-        MUSED_CUDA(cudaMemcpyAsync(D.xlo, D.xlo + (size_t)D.x0 * D.d, bytes, cudaMemcpyDeviceToDevice, st));
-        MUSED_CUDA(cudaMemcpyAsync(D.norm2, D.norm2 + D.x0, (size_t)E.pend * sizeof(double), cudaMemcpyDeviceToDevice, st));
+        // cudaMemcpyAsync needs disjoint ranges: move in pieces of at most x0 rows, front to back (dst < src, so a
+        // piece never overwrites rows that are still to be moved)
+        for (int k = 0; k < E.K; ++k) {
+            const size_t base = (size_t)k * D.xrows;
+            for (int done = 0; done < E.pend; done += D.x0) {
+                const int r = std::min(D.x0, E.pend - done);
+                const size_t bytes = (size_t)r * D.d * sizeof(float);
+                MUSED_CUDA(cudaMemcpyAsync(D.xhi + (base + done) * D.d, D.xhi + (base + D.x0 + done) * D.d, bytes, cudaMemcpyDeviceToDevice, st));
+                MUSED_CUDA(cudaMemcpyAsync(D.xlo + (base + done) * D.d, D.xlo + (base + D.x0 + done) * D.d, bytes, cudaMemcpyDeviceToDevice, st));
+                MUSED_CUDA(cudaMemcpyAsync(D.norm2 + base + done, D.norm2 + base + D.x0 + done, (size_t)r * sizeof(double), cudaMemcpyDeviceToDevice, st));
+            }
+        }
     }
     D.x0 = 0;
     return 0;
 }
 
-int bengine_fit(BEngine* Ep, const void* rows, long long n_rows, long long ld, int dtype, int where,
-                cudaStream_t st) {
+int bengine_fit(BEngine* Ep, const void* rows, long long n_rows, long long ld, long long stream_stride, int dtype,
+                int where, cudaStream_t st) {
     BEngine& E = *Ep;
     const size_t es = b_dtype_size(dtype);
     MUSED_REQUIRE(es != 0, "unknown dtype %d", dtype);
     MUSED_REQUIRE(n_rows >= 0 && ld >= E.D.d_l, "bad shape: n_rows=%lld ld=%lld d=%lld", n_rows, ld, E.D.d_l);
     MUSED_REQUIRE(rows != nullptr || n_rows == 0, "rows is NULL");
+    MUSED_REQUIRE(E.K == 1 || stream_stride >= n_rows * ld, "stream_stride %lld overlaps the streams (n_rows %lld x ld %lld)",
+                  stream_stride, n_rows, ld);
     MUSED_CUDA(cudaSetDevice(E.device));
     const long long d = E.D.d_l;
-    const long long host_rows = (long long)(E.raw_bytes / ((size_t)d * es));
+    const long long host_rows = E.raw_rows;
     long long fed = 0;
     while (fed < n_rows) {
-        // a block of caller rows that is resident on the device
+        // a block of caller rows (of every stream) that is resident on the device
         long long blk = n_rows - fed;
         const char* src = (const char*)rows + (size_t)fed * ld * es;
         const void* dev = src;
-        long long dev_ld = ld;
+        long long dev_ld = ld, dev_ss = stream_stride;
         if (where == MUSED_HOST) {
             blk = std::min(blk, host_rows);
-            if (ld == d) MUSED_CUDA(cudaMemcpyAsync(E.raw, src, (size_t)blk * d * es, cudaMemcpyHostToDevice, st));
-            else MUSED_CUDA(cudaMemcpy2DAsync(E.raw, (size_t)d * es, src, (size_t)ld * es, (size_t)d * es, (size_t)blk, cudaMemcpyHostToDevice, st));
+            for (int k = 0; k < E.K; ++k)
+                MUSED_CUDA(cudaMemcpy2DAsync(E.raw + (size_t)k * host_rows * d * es, (size_t)d * es,
+                                             src + (size_t)k * stream_stride * es, (size_t)ld * es, (size_t)d * es,
+                                             (size_t)blk, cudaMemcpyHostToDevice, st));
             dev = E.raw;
             dev_ld = d;
+            dev_ss = host_rows * d;
         }
         long long off = 0;
         while (off < blk) {
@@ -641,7 +677,7 @@ int bengine_fit(BEngine* Ep, const void* rows, long long n_rows, long long ld, i
                 space = E.sb_rows - E.pend;
             }
             const long long m = std::min(blk - off, space);
-            int rc = stage_rows(E, (const char*)dev + (size_t)off * dev_ld * es, m, dev_ld, dtype, false, st);
+            int rc = stage_rows(E, (const char*)dev + (size_t)off * dev_ld * es, m, dev_ld, dev_ss, dtype, false, st);
             if (rc) return rc;
             off += m;
             // ... then fold them chunk by chunk
@@ -659,31 +695,36 @@ int bengine_fit(BEngine* Ep, const void* rows, long long n_rows, long long ld, i
         fed += blk;
         if (where == MUSED_HOST) MUSED_CUDA(cudaStreamSynchronize(st));   // E.raw is reused / caller buffer is free
     }
+    E.last_stream = st;
     return 0;
 }
 
+int bengine_streams(BEngine* E) { return E->K; }
 unsigned long long bengine_time(BEngine* E) { return E->time; }
 int bengine_qcap(BEngine* E) { return E->D.capn; }
 
 static int b_read_slots(BEngine& E, std::vector<BSlot>& sl) {
     sl.resize(std::max(E.D.S, 1));
     MUSED_CUDA(cudaSetDevice(E.device));
+    MUSED_CUDA(cudaStreamSynchronize(E.last_stream));      // the kernels of the last fit() may still be running
     MUSED_CUDA(cudaMemcpy(sl.data(), E.D.slots, sizeof(BSlot) * sl.size(), cudaMemcpyDeviceToHost));
     return 0;
 }
-static int b_fd_slot(const BEngine& E, int level) {
+static int b_fd_slot(const BEngine& E, int level, int stream_k = 0) {
     // the chunk that contains row `done` decided the period: period = t_a / N of the last chunk;
     // rows are only folded in whole chunks, so done / N is that period once a boundary row was folded
     const unsigned long long p = E.done / E.D.N;
-    return 2 * level + (int)(p & 1ull);
+    return stream_k * E.D.S1 + 2 * level + (int)(p & 1ull);
 }
 
-int bengine_size(BEngine* E, long long* n) {
+int bengine_size(BEngine* E, int stream_k, long long* n) {
+    MUSED_REQUIRE(stream_k >= 0 && stream_k < E->K, "stream %d out of range (n_streams %d)", stream_k, E->K);
     std::vector<BSlot> sl;
     int rc = b_read_slots(*E, sl);
     if (rc) return rc;
     long long tot = 0;
-    for (int j = 0; j < E->n_levels; ++j) tot += sl[2 * j].q_len + sl[2 * j + 1].q_len + 2ll * E->D.ell_l;
+    const int o = stream_k * E->D.S1;
+    for (int j = 0; j < E->n_levels; ++j) tot += sl[o + 2 * j].q_len + sl[o + 2 * j + 1].q_len + 2ll * E->D.ell_l;
     *n = tot;
     return 0;
 }
@@ -706,7 +747,7 @@ static int b_copy_out_2d(double* dst, const double* src, size_t rows, size_t col
 // SeqBasedSWFD.get, first half: level choice (seq_based_swfd.py:83-98), stack
 // [C; snapshots] of the chosen level and its float64 Gram.  *ng = rows of the
 // stack, 0 when the level has no snapshots (no Gram needed).
-static int b_get_begin(BEngine* Ep, int* level, int* ng_out, bool with_gram, cudaStream_t st) {
+static int b_get_begin(BEngine* Ep, int stream_k, int* level, int* ng_out, bool with_gram, cudaStream_t st) {
     BEngine& E = *Ep;
     BDev& D = E.D;
     if (E.n_levels == 0) {
@@ -714,6 +755,7 @@ static int b_get_begin(BEngine* Ep, int* level, int* ng_out, bool with_gram, cud
         return MUSED_ERR_STATE;
     }
     MUSED_REQUIRE(E.pend == 0, "get_begin: the open chunk must be closed first");
+    MUSED_REQUIRE(stream_k >= 0 && stream_k < E.K, "stream %d out of range (n_streams %d)", stream_k, E.K);
     MUSED_CUDA(cudaSetDevice(E.device));
     MUSED_CUDA(cudaStreamSynchronize(st));
     std::vector<BSlot> sl;
@@ -722,14 +764,14 @@ static int b_get_begin(BEngine* Ep, int* level, int* ng_out, bool with_gram, cud
     int rj = 0;
     const unsigned long long time = E.time, N = D.N;
     for (int j = 0; j < E.n_levels; ++j) {
-        const int s = b_fd_slot(E, j);
+        const int s = b_fd_slot(E, j, stream_k);
         if (sl[s].q_len == 0) break;
         unsigned long long head_s = 0;
         MUSED_CUDA(cudaMemcpy(&head_s, D.ringS + (size_t)s * D.capn + sl[s].q_head, 8, cudaMemcpyDeviceToHost));
         if (time - head_s >= std::min(N - 1ull, time - 1ull)) { rj = j; break; }
     }
     if (level) *level = rj;
-    const int s = b_fd_slot(E, rj);
+    const int s = b_fd_slot(E, rj, stream_k);
     E.q_slot = s;
     E.q_ng = 0;
     if (sl[s].q_len != 0) {
@@ -747,7 +789,7 @@ static int b_get_begin(BEngine* Ep, int* level, int* ng_out, bool with_gram, cud
 }
 
 int bengine_get_begin(BEngine* Ep, int* level, int* ng_out, cudaStream_t st) {
-    return b_get_begin(Ep, level, ng_out, true, st);
+    return b_get_begin(Ep, 0, level, ng_out, true, st);
 }
 
 int bengine_get_finish(BEngine* Ep, double* sketch, double* sigma2, double* vt, double* delta, int where,
@@ -775,7 +817,7 @@ int bengine_get_finish(BEngine* Ep, double* sketch, double* sigma2, double* vt, 
     return 0;
 }
 
-int bengine_get(BEngine* Ep, double* sketch, double* sigma2, double* vt, double* delta, int* level,
+int bengine_get(BEngine* Ep, int stream_k, double* sketch, double* sigma2, double* vt, double* delta, int* level,
                 int where, cudaStream_t st) {
     BEngine& E = *Ep;
     if (E.n_levels == 0) {
@@ -786,7 +828,7 @@ int bengine_get(BEngine* Ep, double* sketch, double* sigma2, double* vt, double*
     int rc = process_chunk(E, st);      // get() closes the open chunk (the reference flushes on get, too)
     if (rc) return rc;
     int ng = 0;
-    if ((rc = b_get_begin(Ep, level, &ng, false, st))) return rc;
+    if ((rc = b_get_begin(Ep, stream_k, level, &ng, false, st))) return rc;
     return bengine_get_finish(Ep, sketch, sigma2, vt, delta, where, st);
 }
 
@@ -820,16 +862,18 @@ int bengine_stage(BEngine* Ep, const void* rows, long long m, long long ld, int 
         dev = E.raw;
         dev_ld = E.D.d_l;
     }
-    int rc = stage_rows(E, dev, m, dev_ld, dtype, true, st);
+    MUSED_REQUIRE(E.K == 1, "the phase API drives one stream");
+    int rc = stage_rows(E, dev, m, dev_ld, 0, dtype, true, st);
     if (rc) return rc;
     E.time += (unsigned long long)m;
     if (where == MUSED_HOST) MUSED_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
 
-int bengine_debug(BEngine* Ep, double* scal, double* sigma2, unsigned long long* q_s,
+int bengine_debug(BEngine* Ep, int stream_k, double* scal, double* sigma2, unsigned long long* q_s,
                   unsigned long long* q_t, long long q_cap) {
     BEngine& E = *Ep;
+    MUSED_REQUIRE(stream_k >= 0 && stream_k < E.K, "stream %d out of range (n_streams %d)", stream_k, E.K);
     std::vector<BSlot> sl;
     int rc = b_read_slots(E, sl);
     if (rc) return rc;
@@ -837,7 +881,7 @@ int bengine_debug(BEngine* Ep, double* scal, double* sigma2, unsigned long long*
     std::vector<unsigned long long> rs(capn), rt(capn);
     for (int j = 0; j < E.n_levels; ++j) {
         for (int side = 0; side < 2; ++side) {
-            const int fd = b_fd_slot(E, j);
+            const int fd = b_fd_slot(E, j, stream_k);
             const int s = side == 0 ? fd : (fd ^ 1);
             const int o = 2 * j + side;
             if (scal) {

@@ -9,7 +9,9 @@ namespace mused {
 constexpr int BS_MAX_ELL = 128;
 
 struct BDev {
-    int S, ell, n2, capn, KS;  // ell = PHYSICAL sketch rows (16 / 32 / 64 / 128), n2 = 2 ell
+    int S, ell, n2, capn, KS;  // S = FD instances of ALL streams; ell = PHYSICAL sketch rows (16 / 32 / 64 / 128), n2 = 2 ell
+    int S1;                    // FD instances per stream (2 per level); instance s belongs to stream s / S1
+    long long xrows;           // rows of one stream's staging planes (stream k starts at row k * xrows)
     int ell_l;                 // the caller's sketch_dim <= ell; rows ell_l .. ell-1 of every sketch stay zero
     int x0;                    // row of the staging planes where the open chunk starts
     long long d;               // PHYSICAL row length (multiple of 32); columns d_l .. d-1 stay zero
@@ -18,8 +20,8 @@ struct BDev {
     double qcap;
     BSlot* slots;
     float *skhi, *sklo;        // [S][2][ell][d] sketch planes (TF32 hi / lo), ping-pong
-    float *xhi, *xlo;          // [stage rows + ell][d] staged rows of a fit() call; the open chunk starts at row x0
-    double* norm2;             // [stage rows + ell] ||x||^2 of the staged rows
+    float *xhi, *xlo;          // [K][xrows = stage rows + ell][d] staged rows of a fit() call; the open chunk starts at row x0
+    double* norm2;             // [K][xrows] ||x||^2 of the staged rows
     unsigned char* mask;       // [S][ell] 1 = chunk row is a raw snapshot at this instance's level
     float* Gp;                 // [S][KS][n2][n2] split-K partials of K2
     double* G;                 // [S][n2][n2] their float64 sum (the buffer a column-sharded run allreduces)
@@ -35,16 +37,18 @@ struct BDev {
 struct BEngine;
 
 int bengine_create(BEngine** out, long long N, long long d, long long ell, double beta, int n_levels,
-                   const double* thr, int device, long long batch);
+                   const double* thr, int device, long long batch, int n_streams);
 void bengine_destroy(BEngine* E);
-int bengine_fit(BEngine* E, const void* rows, long long n_rows, long long ld, int dtype, int where,
-                cudaStream_t st);
-int bengine_get(BEngine* E, double* sketch, double* sigma2, double* vt, double* delta, int* level,
+// n_rows rows for EVERY stream: stream k's rows start at rows + k * stream_stride elements
+int bengine_fit(BEngine* E, const void* rows, long long n_rows, long long ld, long long stream_stride, int dtype,
                 int where, cudaStream_t st);
-int bengine_size(BEngine* E, long long* n);
+int bengine_get(BEngine* E, int stream_k, double* sketch, double* sigma2, double* vt, double* delta, int* level,
+                int where, cudaStream_t st);
+int bengine_size(BEngine* E, int stream_k, long long* n);
+int bengine_streams(BEngine* E);
 unsigned long long bengine_time(BEngine* E);
 int bengine_qcap(BEngine* E);
-int bengine_debug(BEngine* E, double* scal, double* sigma2, unsigned long long* q_s,
+int bengine_debug(BEngine* E, int stream_k, double* scal, double* sigma2, unsigned long long* q_s,
                   unsigned long long* q_t, long long q_cap);
 // CUDA-event time per kernel class since the last reset: ms[5] = {stage, book, gram, eig, rotate},
 // chunks processed.  enable: 1 arm+reset, 0 disarm+reset, -1 read only.

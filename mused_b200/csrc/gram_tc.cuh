@@ -27,6 +27,7 @@ struct GramArgs {
     float* Gp;            // [S][KS][n2][n2]
     int ell, KS, kblocks; // kblocks = k-blocks of 32 floats per CTA
     int x0;               // first row of the open chunk in the staging planes
+    int S1, xrows;        // instances per stream, plane rows per stream
 };
 
 template <int N2>
@@ -56,6 +57,7 @@ k_gram_tc(const __grid_constant__ CUtensorMap tm_sk_hi, const __grid_constant__ 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ks = blockIdx.x, s = blockIdx.y;
     const int cur = A.slots[s].cur;
+    const int xrow = (s / A.S1) * A.xrows + A.x0;
 
     if (warp == 0 && lane == 0) {
         umma::tma_prefetch_desc(&tm_sk_hi);
@@ -86,9 +88,9 @@ k_gram_tc(const __grid_constant__ CUtensorMap tm_sk_hi, const __grid_constant__ 
                 const int col = (ks * A.kblocks + kb) * 32;
                 umma::mbar_expect_tx(&full[st], 2 * N2 * 128);
                 umma::tma_load_2d(hi, &tm_sk_hi, &full[st], col, row_sk);
-                umma::tma_load_2d(hi + ELL * 128, &tm_x_hi, &full[st], col, A.x0);
+                umma::tma_load_2d(hi + ELL * 128, &tm_x_hi, &full[st], col, xrow);
                 umma::tma_load_2d(lo, &tm_sk_lo, &full[st], col, row_sk);
-                umma::tma_load_2d(lo + ELL * 128, &tm_x_lo, &full[st], col, A.x0);
+                umma::tma_load_2d(lo + ELL * 128, &tm_x_lo, &full[st], col, xrow);
             }
         }
     } else if (warp == 1) {

@@ -46,7 +46,7 @@ k_rotate_tc(const __grid_constant__ CUtensorMap tm_t_hi, const __grid_constant__
         const long long c = (long long)blockIdx.x * RotCfg::NT + 4 * (threadIdx.x & 31);
         if (c >= D.d) return;
         for (int k = wi; k < nraw; k += nw) {
-            const size_t xr = (size_t)(D.x0 + rl[k]) * D.d + c;
+            const size_t xr = ((size_t)(s / D.S1) * D.xrows + D.x0 + rl[k]) * D.d + c;
             const float4 h = *reinterpret_cast<const float4*>(D.xhi + xr);
             const float4 l = *reinterpret_cast<const float4*>(D.xlo + xr);
             *reinterpret_cast<float4*>(D.ringV + ((size_t)s * D.capn + rl[D.ell + k]) * D.d + c) =
@@ -68,6 +68,7 @@ k_rotate_tc(const __grid_constant__ CUtensorMap tm_t_hi, const __grid_constant__
     const int ell = D.ell, n2 = D.n2;
     const int c0 = blockIdx.x * C::NT;
     const int src = sl.src;
+    const int xbase = (s / D.S1) * (int)D.xrows + D.x0;
     const int kblocks = n2 / C::KB;                  // n2 = 32, 64, 128, 256
     const int brows = ell < C::KB ? ell : C::KB;     // rows of one R box (a box never mixes sketch and chunk rows)
 
@@ -114,8 +115,8 @@ k_rotate_tc(const __grid_constant__ CUtensorMap tm_t_hi, const __grid_constant__
                             umma::tma_load_2d(b_hi + off, &tm_sk_hi, &full[st], c0 + ch * 32, row_sk + k);
                             umma::tma_load_2d(b_lo + off, &tm_sk_lo, &full[st], c0 + ch * 32, row_sk + k);
                         } else {
-                            umma::tma_load_2d(b_hi + off, &tm_x_hi, &full[st], c0 + ch * 32, D.x0 + k - ell);
-                            umma::tma_load_2d(b_lo + off, &tm_x_lo, &full[st], c0 + ch * 32, D.x0 + k - ell);
+                            umma::tma_load_2d(b_hi + off, &tm_x_hi, &full[st], c0 + ch * 32, xbase + k - ell);
+                            umma::tma_load_2d(b_lo + off, &tm_x_lo, &full[st], c0 + ch * 32, xbase + k - ell);
                         }
                     }
                 }

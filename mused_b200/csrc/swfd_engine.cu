@@ -806,11 +806,12 @@ int mused_swfd_create(mused_swfd_t** out, const mused_swfd_cfg* cfg) {
     if (cfg->schedule == MUSED_SCHEDULE_BATCHED) {
         BEngine* B = nullptr;
         int rc = bengine_create(&B, cfg->N, cfg->d, cfg->ell, cfg->beta, cfg->n_levels, cfg->thresholds,
-                                cfg->device, cfg->batch_rows);
+                                cfg->device, cfg->batch_rows, cfg->n_streams > 0 ? cfg->n_streams : 1);
         if (rc) return rc;
         *out = new mused_swfd{nullptr, B};
         return 0;
     }
+    MUSED_REQUIRE(cfg->n_streams <= 1, "n_streams > 1 (independent streams batched per GPU) is served by schedule=batched");
     Engine* E = nullptr;
     int rc = engine_create(&E, cfg->N, cfg->d, cfg->ell, cfg->beta, cfg->n_levels, cfg->thresholds,
                            cfg->device, cfg->cluster, cfg->chunk_rows, false, 0.0);
@@ -832,8 +833,35 @@ int mused_swfd_destroy(mused_swfd_t* h) {
 int mused_swfd_fit(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld, int dtype,
                    int where, void* stream) {
     MUSED_REQUIRE(h, "NULL handle");
-    if (h->B) return bengine_fit(h->B, rows, n_rows, ld, dtype, where, (cudaStream_t)stream);
+    if (h->B) {
+        MUSED_REQUIRE(bengine_streams(h->B) == 1, "this handle batches %d streams: use mused_swfd_fit_streams", bengine_streams(h->B));
+        return bengine_fit(h->B, rows, n_rows, ld, 0, dtype, where, (cudaStream_t)stream);
+    }
     return engine_feed(*h->E, rows, n_rows, ld, dtype, where, MODE_SEQ, 0, (cudaStream_t)stream);
+}
+int mused_swfd_fit_streams(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld, int64_t stream_stride,
+                           int dtype, int where, void* stream) {
+    MUSED_REQUIRE(h, "NULL handle");
+    MUSED_REQUIRE(h->B, "independent streams batched per GPU are served by schedule=batched");
+    return bengine_fit(h->B, rows, n_rows, ld, stream_stride, dtype, where, (cudaStream_t)stream);
+}
+int mused_swfd_get_stream(mused_swfd_t* h, int32_t k, double* sketch, double* sigma2, double* vt, double* delta,
+                          int32_t* level, int where, void* stream) {
+    MUSED_REQUIRE(h && sketch && sigma2, "NULL argument");
+    MUSED_REQUIRE(h->B, "independent streams batched per GPU are served by schedule=batched");
+    return bengine_get(h->B, k, sketch, sigma2, vt, delta, level, where, (cudaStream_t)stream);
+}
+int mused_swfd_size_stream(mused_swfd_t* h, int32_t k, int64_t* n) {
+    MUSED_REQUIRE(h && n && h->B, "NULL argument / not a batched handle");
+    long long v = 0;
+    int rc = bengine_size(h->B, k, &v);
+    *n = v;
+    return rc;
+}
+int mused_swfd_debug_stream(mused_swfd_t* h, int32_t k, double* scal, double* sigma2, uint64_t* q_s, uint64_t* q_t,
+                            int64_t q_cap) {
+    MUSED_REQUIRE(h && h->B, "NULL argument / not a batched handle");
+    return bengine_debug(h->B, k, scal, sigma2, (unsigned long long*)q_s, (unsigned long long*)q_t, q_cap);
 }
 int mused_swfd_fit_timed(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld, int dtype,
                          int where, const uint64_t* times, void* stream) {
@@ -972,7 +1000,7 @@ static int read_slots(Engine& E, std::vector<Slot>& sl) {
 int mused_swfd_get(mused_swfd_t* h, double* sketch, double* sigma2, double* vt, double* delta,
                    int32_t* level, int where, void* stream) {
     MUSED_REQUIRE(h && sketch && sigma2, "NULL argument");
-    if (h->B) return bengine_get(h->B, sketch, sigma2, vt, delta, level, where, (cudaStream_t)stream);
+    if (h->B) return bengine_get(h->B, 0, sketch, sigma2, vt, delta, level, where, (cudaStream_t)stream);
     Engine& E = *h->E;
     if (E.n_levels == 0) {  // the reference raises KeyError: 0 here
         set_error("SeqBasedSWFD has zero levels (R <= 1): get() is undefined");
@@ -1003,7 +1031,7 @@ int mused_swfd_get(mused_swfd_t* h, double* sketch, double* sigma2, double* vt, 
 
 int mused_swfd_size(mused_swfd_t* h, int64_t* n) {
     MUSED_REQUIRE(h && n, "NULL argument");
-    if (h->B) { long long v = 0; int rc = bengine_size(h->B, &v); *n = v; return rc; }
+    if (h->B) { long long v = 0; int rc = bengine_size(h->B, 0, &v); *n = v; return rc; }
     std::vector<Slot> sl;
     int rc = read_slots(*h->E, sl);
     if (rc) return rc;
@@ -1017,7 +1045,7 @@ int mused_swfd_size(mused_swfd_t* h, int64_t* n) {
 int mused_swfd_debug(mused_swfd_t* h, double* scal, double* sigma2, uint64_t* q_s, uint64_t* q_t,
                      int64_t q_cap) {
     MUSED_REQUIRE(h, "NULL handle");
-    if (h->B) return bengine_debug(h->B, scal, sigma2, (unsigned long long*)q_s, (unsigned long long*)q_t, q_cap);
+    if (h->B) return bengine_debug(h->B, 0, scal, sigma2, (unsigned long long*)q_s, (unsigned long long*)q_t, q_cap);
     Engine& E = *h->E;
     std::vector<Slot> sl;
     int rc = read_slots(E, sl);

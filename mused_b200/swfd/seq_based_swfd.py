@@ -17,7 +17,7 @@ from .. import _lib
 class SeqBasedSWFD:
     def __init__(self, N: int, R: float, d: int, sketch_dim: int, beta: float = 1.0, *,
                  device: int = 0, cluster: int = 0, chunk_rows: int = 0,
-                 schedule: str = "reference", batch_rows: int = 0, **kwargs):
+                 schedule: str = "reference", batch_rows: int = 0, n_streams: int = 1, **kwargs):
         """Sliding Window on Frequent Directions (seq_based_swfd.py:12-44).
 
         Args (reference): N window size, R upper bound of squared row norm,
@@ -54,7 +54,8 @@ class SeqBasedSWFD:
         self.schedule = schedule
         cfg = _lib.SwfdCfg(int(N), self.d, self.sketch_dim, float(beta), len(thr), arr,
                            int(device), int(cluster), int(chunk_rows),
-                           _lib.SCHEDULES[schedule], int(batch_rows))
+                           _lib.SCHEDULES[schedule], int(batch_rows), int(n_streams))
+        self.n_streams = int(n_streams)
         self._h = C.c_void_p()
         _lib.check(lib.mused_swfd_create(C.byref(self._h), C.byref(cfg)))
         self._lib = lib
@@ -101,8 +102,9 @@ class SeqBasedSWFD:
         _lib.check(self._lib.mused_swfd_time(self._h, C.byref(t)))
         return np.uint64(t.value)
 
-    def debug_state(self):
-        """Per FD instance state in the layout of oracle.swfd_oracle.SeqSWFD.debug_state."""
+    def debug_state(self, stream=None):
+        """Per FD instance state in the layout of oracle.swfd_oracle.SeqSWFD.debug_state
+        (``stream`` = index of the stream of a MultiStreamSWFD)."""
         S = 2 * len(self.thresholds)
         cap = C.c_int64(0)
         _lib.check(self._lib.mused_swfd_queue_capacity(self._h, C.byref(cap)))
@@ -111,8 +113,12 @@ class SeqBasedSWFD:
         s2 = np.zeros((max(S, 1), self.sketch_dim))
         qs = np.zeros((max(S, 1), cap), dtype=np.uint64)
         qt = np.zeros((max(S, 1), cap), dtype=np.uint64)
-        _lib.check(self._lib.mused_swfd_debug(self._h, scal.ctypes.data, s2.ctypes.data,
-                                              qs.ctypes.data, qt.ctypes.data, cap))
+        if stream is None:
+            _lib.check(self._lib.mused_swfd_debug(self._h, scal.ctypes.data, s2.ctypes.data,
+                                                  qs.ctypes.data, qt.ctypes.data, cap))
+        else:
+            _lib.check(self._lib.mused_swfd_debug_stream(self._h, int(stream), scal.ctypes.data, s2.ctypes.data,
+                                                         qs.ctypes.data, qt.ctypes.data, cap))
         out = []
         for o in range(S):
             ql = int(scal[o, 4])
@@ -167,6 +173,67 @@ class SeqBasedSWFD:
             pass
 
 
+class MultiStreamSWFD(SeqBasedSWFD):
+    """K independent SeqBasedSWFD sketches behind one handle (north_star: "independent streams and windows
+    are batched per GPU"; BASELINE configs[4] "64 independent windows batched per GPU").  Every stream has the
+    semantics of ``SeqBasedSWFD(N, R, d, sketch_dim, beta, schedule="batched")`` on its own rows
+    (seq_based_swfd.py:11-103) and shares nothing with the others; the engine advances all of them in
+    lock-step, one K1..K5 launch sequence per chunk for the K x 2 x levels FD instances
+    (C ABI: mused_swfd_cfg.n_streams, mused_swfd_fit_streams / get_stream / size_stream)."""
+
+    def __init__(self, n_streams: int, N: int, R: float, d: int, sketch_dim: int, beta: float = 1.0, *,
+                 device: int = 0, batch_rows: int = 0, **kwargs):
+        super().__init__(N, R, d, sketch_dim, beta, device=device, schedule="batched", batch_rows=batch_rows,
+                         n_streams=n_streams, **kwargs)
+
+    def fit(self, X):
+        """X: (K, n, d) -- n consecutive rows for every stream (numpy or torch, host or CUDA)."""
+        try:
+            import torch
+        except Exception:  # pragma: no cover
+            torch = None
+        K = self.n_streams
+        if torch is not None and isinstance(X, torch.Tensor):
+            if X.dim() != 3 or X.shape[0] != K or X.shape[2] != self.d:
+                raise ValueError("expected (n_streams=%d, n, d=%d) rows, got %s" % (K, self.d, tuple(X.shape)))
+            if X.stride(2) != 1 or (X.shape[1] > 1 and X.stride(1) < self.d):
+                X = X.contiguous()
+            keep, ptr, n, ld, dt, where = _lib.rows_arg(X[0], self.d)
+            stride = X.stride(0) if K > 1 else n * ld
+            keep = X
+        else:
+            X = np.asarray(X)
+            if X.ndim != 3 or X.shape[0] != K or X.shape[2] != self.d:
+                raise ValueError("expected (n_streams=%d, n, d=%d) rows, got %s" % (K, self.d, X.shape))
+            if X.dtype not in _lib._NP_DTYPES:
+                X = X.astype(np.float64)
+            X = np.ascontiguousarray(X)
+            keep, ptr, n, ld, dt, where = _lib.rows_arg(X[0], self.d)
+            stride = X.strides[0] // X.itemsize
+            keep = X
+        _lib.check(self._lib.mused_swfd_fit_streams(self._h, ptr, n, ld, stride, dt, where,
+                                                    _lib.current_stream(self._device)))
+        del keep
+
+    def get(self, stream=0):
+        """(sketch, sigma_squared, Vt, delta) of stream ``stream`` (seq_based_swfd.py:83-100)."""
+        ell, d = self.sketch_dim, self.d
+        sketch, s2, vt = np.empty((ell, d)), np.empty(ell), np.empty((ell, d))
+        delta, level = C.c_double(0.0), C.c_int32(0)
+        if self.logR <= 0:
+            raise KeyError(0)
+        _lib.check(self._lib.mused_swfd_get_stream(self._h, int(stream), sketch.ctypes.data, s2.ctypes.data,
+                                                   vt.ctypes.data, C.byref(delta), C.byref(level), _lib.HOST,
+                                                   _lib.current_stream(self._device)))
+        self.last_level = int(level.value)
+        return sketch, s2, vt, float(delta.value)
+
+    def get_size(self, stream=0):
+        n = C.c_int64(0)
+        _lib.check(self._lib.mused_swfd_size_stream(self._h, int(stream), C.byref(n)))
+        return int(n.value)
+
+
 class TimeBasedSWFD(SeqBasedSWFD):
     """TimeBasedSWFD on the B200 engine (swfd/seq_based_swfd.py:106-207): rows carry an explicit
     arrival time, the ladder has ceil(log2(N R / sketch_dim)) levels with dump thresholds 2^j
@@ -193,7 +260,8 @@ class TimeBasedSWFD(SeqBasedSWFD):
         lib = _lib.load()
         arr = (C.c_double * max(1, len(thr)))(*thr)
         cfg = _lib.SwfdCfg(int(N), self.d, self.sketch_dim, float(beta), len(thr), arr,
-                           int(device), int(cluster), int(chunk_rows), _lib.SCHEDULES["reference"], 0)
+                           int(device), int(cluster), int(chunk_rows), _lib.SCHEDULES["reference"], 0, 1)
+        self.n_streams = 1
         self._h = C.c_void_p()
         _lib.check(lib.mused_swfd_create(C.byref(self._h), C.byref(cfg)))
         self._lib = lib

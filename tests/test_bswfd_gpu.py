@@ -222,3 +222,38 @@ def test_batched_engine_degenerate_and_scaled_streams(kind):
                 assert g["q_t"] == o["q_t"] and g["q_s"] == o["q_s"]
                 assert (g["n_flush"], g["n_dump"], g["n_raw"]) == (o["n_flush"], o["n_dump"], o["n_raw"])
     gpu.close()
+
+
+@pytest.mark.parametrize("shape", [(3, 64, 256, 700, 1500), (5, 50, 600, 400, 900), (2, 128, 1024, 1000, 1300)])
+def test_multi_stream_engine_equals_solo_runs(shape):
+    """n_streams sketches behind one handle (one launch sequence for all K x 2 x levels instances): stream k's
+    sketch, sigma^2, delta, level, size and snapshot stamps equal a solo SeqBasedSWFD(schedule="batched") fed
+    the same rows, bit for bit (same kernels, same per-instance arithmetic order)."""
+    from mused_b200.swfd import SeqBasedSWFD, MultiStreamSWFD
+    K, ell, d, N, n = shape
+    A = np.stack([synth.lowrank_stream(n, d, seed=10 + k, scale=1.0 + 0.5 * k) for k in range(K)])
+    R = float(max(synth.row_norm2_max(A[k]) for k in range(K)))
+    ms = MultiStreamSWFD(K, N, R, d, ell)
+    solos = [SeqBasedSWFD(N, R, d, ell, schedule="batched") for _ in range(K)]
+    Ad = torch.as_tensor(A).cuda()
+    cuts = [0, 1, 130, 131, n // 2, n]
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        if (a // 7) % 2:
+            ms.fit(Ad[:, a:b])                       # device rows (strided view)
+        else:
+            ms.fit(A[:, a:b])                        # host rows
+        for k in range(K):
+            solos[k].fit(Ad[k, a:b])
+        for k in range(K):
+            assert ms.get_size(k) == solos[k].get_size()
+            Bm, s2m, vtm, dm = ms.get(k)
+            lm = ms.last_level
+            Bs, s2s, vts, ds = solos[k].get()
+            assert lm == solos[k].last_level
+            assert np.array_equal(s2m, s2s) and dm == ds
+            assert np.array_equal(Bm, Bs)
+    for k in range(K):
+        sm, ss = ms.debug_state(k), solos[k].debug_state()
+        assert [o["q_t"] for o in sm] == [o["q_t"] for o in ss]
+        assert [o["q_s"] for o in sm] == [o["q_s"] for o in ss]
+        assert [o["last_dump_time"] for o in sm] == [o["last_dump_time"] for o in ss]

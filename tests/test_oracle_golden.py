@@ -135,3 +135,27 @@ def test_cosine_assign_oracle_properties():
     assert np.all(labels == -1)
     labels, best, _ = ops_oracle.cosine_assign(np.zeros((2, 33)), C, 0.0)    # zero rows: cosine 0
     assert np.all(best == 0) and np.all(labels == 0)
+
+
+def test_oracle_reproduces_full_length_reference_fixture_prefix(golden_dir):
+    """tests/golden/full_c0.npz was produced by the UNMODIFIED reference on configs[0] (20k x 512, l=64,
+    N=2000); the restatement must reproduce its first two windows bit for bit (sigma^2, delta, size, level)."""
+    import hashlib
+    from mused_b200 import synth
+    p = os.path.join(golden_dir, "full_c0.npz")
+    if not os.path.exists(p):
+        pytest.skip("full_c0.npz missing")
+    g = np.load(p)
+    n = 2 * int(g["qstep"])
+    A, labels, centres = synth.event_stream(int(g["n"]), blocks=(256, 192, 32, 32), n_events=150, seed=0)
+    assert hashlib.sha256(np.ascontiguousarray(A).tobytes()).hexdigest() == str(g["sha_A"])
+    A64 = A[:n].astype(np.float64)
+    ora = so.SeqSWFD(int(g["N"]), float(g["R"]), A.shape[1], int(g["ell"]))
+    for qi in range(2):
+        for t in range(qi * int(g["qstep"]), (qi + 1) * int(g["qstep"])):
+            ora.fit(A64[t:t + 1])
+        assert ora.pick_level() == int(g["level"][qi]) and ora.get_size() == int(g["size"][qi])
+        B, s2, vt, delta = ora.get()
+        assert np.array_equal(s2, g["sigma2"][qi]) and delta == g["delta"][qi]
+        err = so.cov_error(A64[qi * 2000:(qi + 1) * 2000], B)       # BLAS thread count changes the last bits
+        assert abs(err - g["cov_err"][qi]) <= 1e-10 * g["cov_err"][qi]
