@@ -418,6 +418,48 @@ def run_ours(args, rank, local_rank, world):
         best = max(multi["by_streams"].items(), key=lambda kv: kv[1]["value"])
         multi["streams_per_gpu"], multi["value"] = int(best[0]), best[1]["value"]
 
+    # ---------------- column-sharded mode (north_star): d = 16384 split over the `world` ranks, the same
+    # rows on every rank, per chunk two NCCL allreduces (||x||^2, Gram) posted from inside the C ABI on the
+    # engine's stream; strong scaling: the same total work for every N (N = 1: the unsharded engine)
+    sharded = None
+    if args.schedule == "batched" and not args.no_sharded:
+        from mused_b200.sharded import NcclShardedSWFD, shard_bounds
+        DS, wins = 16384, 2
+        gen = torch.Generator(device=dev)
+        gen.manual_seed(1234)                                  # the same stream on every rank
+        Us, _ = torch.linalg.qr(torch.randn(DS, 10, device=dev, generator=gen))
+        Dg = torch.tensor([1.0 - (i - 1) / 10 for i in range(10)], device=dev)
+        lo, hi = shard_bounds(DS, world, rank)
+        Xs = []
+        for w in range(1 + wins):                              # full rows are drawn, this rank keeps its columns
+            S_ = torch.randn(WIN, 10, device=dev, generator=gen) * Dg
+            Z_ = torch.randn(WIN, DS, device=dev, generator=gen)
+            Xw = S_ @ Us.T + Z_ * (1.0 / 40.0)                 # zeta scaled by sqrt(d / 1024): same ||row||^2 as configs[1]
+            Xs.append(Xw[:, lo:hi].contiguous())
+            del S_, Z_, Xw
+        shd = NcclShardedSWFD(WIN, R, DS, ELL, device=local_rank)
+        shd.fit(Xs[0])
+        shd.get(gather=False)
+        barrier()
+        e0.record()
+        for w in range(1, 1 + wins):
+            shd.fit(Xs[w])
+            shd.get(gather=False)
+        e1.record()
+        barrier()
+        ms = max_over_ranks(e0.elapsed_time(e1))
+        na, nb = shd.comm_stats()
+        sharded = {"value": wins * WIN / (ms * 1e-3), "unit": UNIT, "scaling": "strong", "n_gpus": world,
+                   "workload": "SWFD d=16384 l=128 N=10000 low-rank+noise stream, d column-sharded over %d GPU(s), "
+                               "fit + get per window (sketch left sharded)" % world,
+                   "columns_per_gpu": hi - lo, "ms_per_window": ms / wins,
+                   "allreduces_per_window": na / (1 + wins), "allreduce_MB_per_window": nb / (1 + wins) / 1e6,
+                   "collective": "ncclAllReduce(float64 sum) of ||x||^2[rows] and of the Gram [S][2l][2l] per chunk, "
+                                 "posted from the C ABI on the engine's stream"}
+        shd.close()
+        del Xs, shd
+        torch.cuda.empty_cache()
+
     # ---------------- end-to-end arm (`e2e`): host buffers through the public API
     e2e = None
     if not args.no_e2e:
@@ -591,7 +633,7 @@ def run_ours(args, rank, local_rank, world):
                          "FD state is meant to stay L2-resident",
                    "query_level": main_res["level"]},
         "clocks": main_res["clocks"], "multi_stream": multi, "get_ms_per_step": main_res["get_ms"],
-        "cpu_batched_baseline": cpu_b,
+        "cpu_batched_baseline": cpu_b, "sharded": sharded,
         "fit_ms_per_step": main_res["fit_ms"], "assign_ms_per_step": main_res["assign_ms"] if args.phase_times else None, "e2e": e2e, "gpu_launches": main_res["launches"], "roofline": roofline,
         "cpu_baseline": cpu, "cov_error": cov,
         "flushes_per_row": sum(o["n_flush"] for o in st) / float(n_steps * WIN),

@@ -167,6 +167,18 @@ int mused_swfd_profile(mused_swfd_t* h, uint64_t* cycles, int64_t n_inst_cap);
  * and a query as  get_begin -> allreduce-sum query_gram (when n_stack > 0) -> get_finish.
  * Every decision depends on replicated scalars only, so all ranks stay in lock-step.
  * ------------------------------------------------------------------------- */
+/* The same mode with the exchanges INSIDE the library: rank 0 draws a NCCL unique id
+ * (mused_comm_unique_id), the host distributes its bytes (torch.distributed broadcast, MPI, a file ...),
+ * every rank attaches it to its handle before the first row; from then on mused_swfd_fit / mused_swfd_get on
+ * that handle are collective calls (every rank feeds its own columns of the same rows) and post
+ * ncclAllReduce(norm2) and ncclAllReduce(gram) per chunk, ncclAllReduce(query gram) per get(), on the
+ * caller's stream with no host synchronisation.  nccl_path: the libnccl.so.2 to dlopen (NULL = the one
+ * the process already maps, e.g. torch's).  comm_stats: allreduces posted and their payload bytes. */
+int mused_comm_unique_id(void* id_out, int64_t cap, int64_t* n_bytes, const char* nccl_path);
+int mused_swfd_attach_comm(mused_swfd_t* h, const void* unique_id, int64_t n_bytes, int32_t rank, int32_t nranks,
+                           const char* nccl_path);
+int mused_swfd_comm_stats(mused_swfd_t* h, uint64_t* n_allreduce, uint64_t* bytes);
+
 int mused_swfd_chunk_room(mused_swfd_t* h, int64_t* room, int64_t* pending);
 int mused_swfd_stage(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld, int dtype, int where,
                      void* stream);

@@ -46,6 +46,7 @@ SYMBOLS = [
     "mused_fd_dump", "mused_fd_flush", "mused_fd_get",
     "mused_assign", "mused_topk_adjacency", "mused_contingency", "mused_sym_eig",
     "mused_topk_adjacency_f64", "mused_swfd_kernel_gaps", "mused_swfd_fit_timed",
+    "mused_comm_unique_id", "mused_swfd_attach_comm", "mused_swfd_comm_stats",
     "mused_swfd_fit_streams", "mused_swfd_get_stream", "mused_swfd_size_stream", "mused_swfd_debug_stream",
 ]
 
@@ -85,6 +86,9 @@ def load():
     lib.mused_swfd_get_stream.argtypes = [vp, i32, vp, vp, vp, C.POINTER(dbl), C.POINTER(i32), C.c_int, vp]
     lib.mused_swfd_size_stream.argtypes = [vp, i32, C.POINTER(i64)]
     lib.mused_swfd_debug_stream.argtypes = [vp, i32, vp, vp, vp, vp, i64]
+    lib.mused_comm_unique_id.argtypes = [vp, i64, C.POINTER(i64), C.c_char_p]
+    lib.mused_swfd_attach_comm.argtypes = [vp, vp, i64, i32, i32, C.c_char_p]
+    lib.mused_swfd_comm_stats.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.mused_swfd_size.argtypes = [vp, C.POINTER(i64)]
     lib.mused_swfd_time.argtypes = [vp, C.POINTER(C.c_uint64)]
     lib.mused_swfd_debug.argtypes = [vp, vp, vp, vp, vp, i64]

@@ -24,6 +24,26 @@ NVCC_FLAGS = [
 ] + os.environ.get("MUSED_NVCC_EXTRA", "").split()      # e.g. -DMUSED_EIG_PROF (cycle accounting of K3)
 
 
+def _nccl_include():
+    """nccl.h of the NCCL that torch bundles (types and prototypes only; the entry points are dlopen'ed at run time)."""
+    import importlib.util
+    for mod in ("nvidia.nccl", "torch"):
+        try:
+            spec = importlib.util.find_spec(mod)
+        except Exception:
+            spec = None
+        if spec is None or not spec.submodule_search_locations:
+            continue
+        base = list(spec.submodule_search_locations)[0]
+        for cand in (os.path.join(base, "include"), os.path.join(base, "..", "nvidia", "nccl", "include")):
+            if os.path.exists(os.path.join(cand, "nccl.h")):
+                return os.path.abspath(cand)
+    for cand in ("/usr/include", "/usr/local/cuda/include"):
+        if os.path.exists(os.path.join(cand, "nccl.h")):
+            return cand
+    raise RuntimeError("nccl.h not found (torch's nvidia/nccl/include or /usr/include)")
+
+
 def _digest():
     h = hashlib.sha256()
     for root in (CSRC, os.path.join(HERE, "..", "include")):
@@ -51,7 +71,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     for s in srcs:
         o = os.path.splitext(s)[0] + ".o"
         objs.append(o)
-        cmd = [nvcc, *NVCC_FLAGS, "-c", s, "-o", o]
+        cmd = [nvcc, *NVCC_FLAGS, "-I", _nccl_include(), "-c", s, "-o", o]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
             print(" ".join(cmd), flush=True)
@@ -62,7 +82,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             sys.stderr.write(out)
         if p.returncode != 0:
             raise RuntimeError("nvcc failed on %s" % s)
-    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB, *objs, "-lcudart", "-lcuda"]
+    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB, *objs, "-lcudart", "-lcuda", "-ldl"]
     subprocess.run(cmd, check=True)
     with open(STAMP, "w") as f:
         f.write(dig)

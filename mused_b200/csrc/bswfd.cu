@@ -17,6 +17,7 @@
 #include "gram_tc.cuh"
 #include "eig_smem.cuh"
 #include "rotate_tc.cuh"
+#include "nccl_dyn.h"
 
 namespace mused {
 
@@ -249,6 +250,11 @@ struct BEngine {
     double *o_sketch = nullptr, *o_vt = nullptr, *o_s2 = nullptr, *o_delta = nullptr;
     std::vector<void*> allocs;
     cudaStream_t last_stream = nullptr;   // stream of the last fit(): size / debug read the slots behind it
+    // column-sharded mode: this engine holds the columns of ONE rank; the two exchanges of a chunk
+    // (||x||^2 of the rows, the Gram) are NCCL allreduces posted on the engine's stream from here
+    ncclComm_t comm = nullptr;
+    int comm_rank = 0, comm_size = 1;
+    unsigned long long n_allreduce = 0, allreduce_bytes = 0;
     int q_slot = 0, q_ng = 0;         // pending query (get_begin -> get_finish)
     bool q_gram = true;               // get_begin left the stack Gram in Q.G
     bool timing = false;
@@ -273,6 +279,7 @@ struct BEngine {
         return 0;
     }
     ~BEngine() {
+        if (comm && nccl_api().ok()) nccl_api().CommDestroy(comm);
         for (int k = 0; k < 5; ++k)
             for (cudaEvent_t e : ev[k]) cudaEventDestroy(e);
         for (void* p : allocs) cudaFree(p);
@@ -566,7 +573,23 @@ int bengine_chunk_finish(BEngine* Ep, cudaStream_t st) {
     return 0;
 }
 
+static int allreduce_f64(BEngine& E, double* buf, size_t count, cudaStream_t st) {
+    MUSED_NCCL(nccl_api().AllReduce(buf, buf, count, ncclDouble, ncclSum, E.comm, st));
+    E.n_allreduce += 1;
+    E.allreduce_bytes += count * sizeof(double);
+    return 0;
+}
+
 static int process_chunk(BEngine& E, cudaStream_t st) {
+    if (E.comm && E.pend > 0 && E.D.S > 0) {
+        // exchange 1: global ||x||^2 of the chunk's rows (routing rule X@X.T >= threshold, seq_based_swfd.py:77)
+        int rc = allreduce_f64(E, E.D.norm2 + E.D.x0, (size_t)E.pend, st);
+        if (rc) return rc;
+        if ((rc = bengine_chunk_gram(&E, st))) return rc;
+        // exchange 2: G = sum over the column shards, the one real exchange per shrink; same stream, no host sync
+        if ((rc = allreduce_f64(E, E.D.G, (size_t)E.D.S * E.D.n2 * E.D.n2, st))) return rc;
+        return bengine_chunk_finish(&E, st);
+    }
     int rc = bengine_chunk_gram(&E, st);
     if (rc) return rc;
     return bengine_chunk_finish(&E, st);
@@ -828,8 +851,58 @@ int bengine_get(BEngine* Ep, int stream_k, double* sketch, double* sigma2, doubl
     int rc = process_chunk(E, st);      // get() closes the open chunk (the reference flushes on get, too)
     if (rc) return rc;
     int ng = 0;
+    if (E.comm) {
+        // sharded query: float64 Gram of the local columns of the stack, summed over the ranks (only the live
+        // ng x ng block travels: the scratch is addressed with leading dimension ng for this query)
+        const int lda_full = E.Q.lda;
+        if ((rc = b_get_begin(Ep, stream_k, level, &ng, false, st))) return rc;
+        if (ng > 0) {
+            E.Q.lda = ng + (ng & 1);
+            rc = merge_query_gram(E.Q, ng, E.D.d, E.sm_count, st);
+            if (!rc) rc = allreduce_f64(E, E.Q.G, (size_t)E.Q.lda * E.Q.lda, st);
+            E.q_gram = true;
+        }
+        if (!rc) rc = bengine_get_finish(Ep, sketch, sigma2, vt, delta, where, st);
+        E.Q.lda = lda_full;
+        return rc;
+    }
     if ((rc = b_get_begin(Ep, stream_k, level, &ng, false, st))) return rc;
     return bengine_get_finish(Ep, sketch, sigma2, vt, delta, where, st);
+}
+
+int bengine_attach_comm(BEngine* Ep, const void* unique_id, long long id_bytes, int rank, int nranks, const char* nccl_path) {
+    BEngine& E = *Ep;
+    MUSED_REQUIRE(E.K == 1, "the column-sharded mode drives one stream per handle");
+    MUSED_REQUIRE(!E.comm, "a communicator is already attached");
+    MUSED_REQUIRE(unique_id && id_bytes == (long long)sizeof(ncclUniqueId), "unique id must be %zu bytes", sizeof(ncclUniqueId));
+    MUSED_REQUIRE(nranks >= 1 && rank >= 0 && rank < nranks, "bad rank %d of %d", rank, nranks);
+    MUSED_REQUIRE(E.time == 0, "attach the communicator before the first row");
+    std::string err;
+    if (!nccl_load(nccl_path, &err)) { set_error("%s", err.c_str()); return MUSED_ERR_STATE; }
+    MUSED_CUDA(cudaSetDevice(E.device));
+    ncclUniqueId id;
+    memcpy(&id, unique_id, sizeof(id));
+    MUSED_NCCL(nccl_api().CommInitRank(&E.comm, nranks, id, rank));
+    E.comm_rank = rank;
+    E.comm_size = nranks;
+    return 0;
+}
+
+int bengine_comm_stats(BEngine* E, unsigned long long* n, unsigned long long* bytes) {
+    if (n) *n = E->n_allreduce;
+    if (bytes) *bytes = E->allreduce_bytes;
+    return 0;
+}
+
+int nccl_unique_id(void* out, long long cap, long long* n_bytes, const char* nccl_path) {
+    MUSED_REQUIRE(out && cap >= (long long)sizeof(ncclUniqueId), "unique id buffer must hold %zu bytes", sizeof(ncclUniqueId));
+    std::string err;
+    if (!nccl_load(nccl_path, &err)) { set_error("%s", err.c_str()); return MUSED_ERR_STATE; }
+    ncclUniqueId id;
+    MUSED_NCCL(nccl_api().GetUniqueId(&id));
+    memcpy(out, &id, sizeof(id));
+    if (n_bytes) *n_bytes = (long long)sizeof(id);
+    return 0;
 }
 
 long long bengine_room(BEngine* E) { return chunk_room(*E); }

@@ -73,6 +73,11 @@ int bengine_get_begin(BEngine* E, int* level, int* ng, cudaStream_t st);   // op
 int bengine_get_finish(BEngine* E, double* sketch, double* sigma2, double* vt, double* delta, int where,
                        cudaStream_t st);
 
+// Column-sharded mode with the exchanges inside the library (NCCL allreduce on the engine's stream)
+int nccl_unique_id(void* out, long long cap, long long* n_bytes, const char* nccl_path);
+int bengine_attach_comm(BEngine* E, const void* unique_id, long long id_bytes, int rank, int nranks, const char* nccl_path);
+int bengine_comm_stats(BEngine* E, unsigned long long* n, unsigned long long* bytes);
+
 // Shared query tail (swfd_engine.cu): top-l shrink of the float64 stack M (ng x d).
 struct QueryScratch {
     double *M = nullptr, *G = nullptr, *Vq = nullptr, *cs = nullptr, *eval = nullptr, *scr = nullptr;

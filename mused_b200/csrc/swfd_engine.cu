@@ -863,6 +863,26 @@ int mused_swfd_debug_stream(mused_swfd_t* h, int32_t k, double* scal, double* si
     MUSED_REQUIRE(h && h->B, "NULL argument / not a batched handle");
     return bengine_debug(h->B, k, scal, sigma2, (unsigned long long*)q_s, (unsigned long long*)q_t, q_cap);
 }
+int mused_comm_unique_id(void* id_out, int64_t cap, int64_t* n_bytes, const char* nccl_path) {
+    long long n = 0;
+    int rc = nccl_unique_id(id_out, cap, &n, nccl_path);
+    if (n_bytes) *n_bytes = n;
+    return rc;
+}
+int mused_swfd_attach_comm(mused_swfd_t* h, const void* unique_id, int64_t n_bytes, int32_t rank, int32_t nranks,
+                           const char* nccl_path) {
+    MUSED_REQUIRE(h, "NULL handle");
+    MUSED_REQUIRE(h->B, "the column-sharded mode is served by schedule=batched");
+    return bengine_attach_comm(h->B, unique_id, n_bytes, rank, nranks, nccl_path);
+}
+int mused_swfd_comm_stats(mused_swfd_t* h, uint64_t* n_allreduce, uint64_t* bytes) {
+    MUSED_REQUIRE(h && h->B, "NULL argument / not a batched handle");
+    unsigned long long a = 0, b = 0;
+    bengine_comm_stats(h->B, &a, &b);
+    if (n_allreduce) *n_allreduce = a;
+    if (bytes) *bytes = b;
+    return 0;
+}
 int mused_swfd_fit_timed(mused_swfd_t* h, const void* rows, int64_t n_rows, int64_t ld, int dtype,
                          int where, const uint64_t* times, void* stream) {
     MUSED_REQUIRE(h && (times || n_rows == 0), "NULL argument");

@@ -210,3 +210,97 @@ class ColumnShardedSWFD:
     def close(self):
         if hasattr(self.engine, "close"):
             self.engine.close()
+
+
+def find_nccl_library():
+    """The libnccl.so.2 the process should share with torch (its bundled copy); None lets the library fall back
+    to whatever "libnccl.so.2" resolves to."""
+    import importlib.util
+    import os
+    try:
+        spec = importlib.util.find_spec("nvidia.nccl")
+    except Exception:
+        spec = None
+    if spec is not None and spec.submodule_search_locations:
+        p = os.path.join(list(spec.submodule_search_locations)[0], "lib", "libnccl.so.2")
+        if os.path.exists(p):
+            return p
+    return None
+
+
+class NcclShardedSWFD:
+    """``SeqBasedSWFD(N, R, d, sketch_dim, beta)`` with d column-sharded over the ranks of ``process_group`` and
+    BOTH exchanges inside the C library (north_star: "an NCCL-over-NVLink allreduce of only the
+    Gram per shrink"): rank 0 draws a NCCL unique id, torch.distributed broadcasts its 128 bytes, every rank
+    attaches it to its engine; ``fit`` / ``get`` are then collective calls whose per-chunk allreduces
+    (||x||^2, Gram) are posted on the engine's CUDA stream between its kernels -- no Python in the chunk loop,
+    no host synchronisation.  ``torch.distributed`` is plumbing only (bootstrap + the optional all-gather of the
+    result).  Decisions depend on replicated scalars, so the ranks stay in lock-step (seq_based_swfd.py:76-80).
+    """
+
+    def __init__(self, N, R, d, sketch_dim, beta=1.0, *, process_group=None, device=None, **kwargs):
+        import torch
+        import torch.distributed as dist
+        from .swfd import SeqBasedSWFD
+        self.dist, self.group = dist, process_group
+        self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(process_group) if dist.is_initialized() else 0
+        self.N, self.d, self.sketch_dim = int(N), int(d), int(sketch_dim)
+        self.lo, self.hi = shard_bounds(self.d, self.world, self.rank)
+        if device is None:
+            device = torch.cuda.current_device()
+        self.device = int(device)
+        self.sk = SeqBasedSWFD(N, R, self.hi - self.lo, sketch_dim, beta, device=self.device, schedule="batched", **kwargs)
+        self.logR = self.sk.logR
+        self.last_level = 0
+        if self.world > 1:
+            lib = self.sk._lib
+            path = find_nccl_library()
+            cpath = path.encode() if path else None
+            buf = (C.c_ubyte * 256)()
+            n = C.c_int64(128)
+            if self.rank == 0:
+                _lib.check(lib.mused_comm_unique_id(buf, 256, C.byref(n), cpath))
+            t = torch.tensor(list(buf), dtype=torch.uint8, device=torch.device("cuda", self.device))
+            src = dist.get_global_rank(process_group, 0) if process_group is not None else 0
+            dist.broadcast(t, src=src, group=process_group)
+            raw = bytes(t.cpu().tolist())
+            _lib.check(lib.mused_swfd_attach_comm(self.sk._h, raw, int(n.value), self.rank, self.world, cpath))
+
+    def _local(self, X):
+        if X.shape[-1] == self.d and self.world > 1:
+            return X[:, self.lo:self.hi]
+        return X
+
+    def fit(self, X):
+        """Every rank feeds the same rows: whole (n, d) rows (sliced here) or its own (n, hi - lo) columns."""
+        self.sk.fit(self._local(X))
+
+    def get(self, gather=True):
+        sketch, s2, vt, delta = self.sk.get()
+        self.last_level = self.sk.last_level
+        if gather and self.world > 1:
+            import torch
+            dev = torch.device("cuda", self.device)
+            out = []
+            for M in (sketch, vt):
+                t = torch.as_tensor(np.ascontiguousarray(M)).to(dev)
+                parts = [torch.empty_like(t) for _ in range(self.world)]
+                self.dist.all_gather(parts, t, group=self.group)
+                out.append(torch.cat(parts, dim=1).cpu().numpy())
+            sketch, vt = out
+        return sketch, s2, vt, delta
+
+    def comm_stats(self):
+        a, b = C.c_uint64(0), C.c_uint64(0)
+        _lib.check(self.sk._lib.mused_swfd_comm_stats(self.sk._h, C.byref(a), C.byref(b)))
+        return int(a.value), int(b.value)
+
+    def get_size(self):
+        return self.sk.get_size()
+
+    def debug_state(self):
+        return self.sk.debug_state()
+
+    def close(self):
+        self.sk.close()

@@ -42,3 +42,20 @@ def test_phase_api_equals_fit_get_single_rank():
         assert x["q_t"] == y["q_t"] and x["q_s"] == y["q_s"]
     a.close()
     b.close()
+
+
+def test_nccl_sharded_two_ranks_equals_single_gpu():
+    """2 ranks over NCCL (allreduces posted from inside the C ABI): same schedule, sigma within 5e-6, cov-error
+    within 5e-5 relative of the single-GPU batched engine.  Needs 2 GPUs (skipped otherwise)."""
+    import os
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29533", os.path.join(root, "tools", "sharded_check.py"), "64", "2048", "2000", "5000"]
+    p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-3000:]
+    assert "MISMATCH" not in p.stdout and "-> ok" in p.stdout

@@ -1,7 +1,7 @@
-"""2+ ranks, NCCL: column-sharded SWFD (mused_b200.sharded.ColumnShardedSWFD on the
-CUDA shard engine) against the single-GPU batched engine on the same stream.
-  torchrun --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/sharded_check.py
-Prints one line per query (rank 0) and exits non-zero on a mismatch."""
+"""2+ ranks, NCCL: column-sharded SWFD with the allreduces inside the C library
+(mused_b200.sharded.NcclShardedSWFD) against the single-GPU batched engine on the same stream.
+  torchrun --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/sharded_check.py [ell d N n]
+Prints one line per query (rank 0) and exits non-zero on a mismatch (tests/test_sharded_gpu.py runs it)."""
 import os
 import sys
 import time
@@ -13,7 +13,7 @@ import torch.distributed as dist
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from mused_b200 import synth                                   # noqa: E402
-from mused_b200.sharded import ColumnShardedSWFD               # noqa: E402
+from mused_b200.sharded import NcclShardedSWFD                 # noqa: E402
 from mused_b200.swfd import SeqBasedSWFD                        # noqa: E402
 from oracle import swfd_oracle as so                            # noqa: E402
 
@@ -25,7 +25,7 @@ def main():
     ell, d, N, n = (int(x) for x in sys.argv[1:5]) if len(sys.argv) >= 5 else (64, 2048, 2000, 6000)
     A = synth.lowrank_stream(n, d, seed=2, scale=2.0)
     R = synth.row_norm2_max(A)
-    sh = ColumnShardedSWFD(N, R, d, ell, device=lr)
+    sh = NcclShardedSWFD(N, R, d, ell, device=lr)
     one = SeqBasedSWFD(N, R, d, ell, device=lr, schedule="batched") if rank == 0 else None
     Ad = torch.as_tensor(A).cuda()
     ok = True
@@ -54,9 +54,12 @@ def main():
             print("t=%d world=%d cov_err sharded %.6f single %.6f sigma rel %.2e level %d/%d schedule %s -> %s"
                   % (te, world, e_sh, e_1, rel, sh.last_level, one.last_level, "same" if same else "DIFF",
                      "ok" if good else "MISMATCH"), flush=True)
+        else:
+            sh.debug_state()
     if rank == 0:
-        print("sharded fit: %d rows in %.3fs -> %.0f rows/s (d=%d over %d GPUs, %d allreduces)"
-              % (n, t_sh, n / t_sh, d, world, sh.n_allreduce), flush=True)
+        na, nb = sh.comm_stats()
+        print("sharded fit: %d rows in %.3fs -> %.0f rows/s (d=%d over %d GPUs, %d allreduces, %.1f MB)"
+              % (n, t_sh, n / t_sh, d, world, na, nb / 1e6), flush=True)
     flag = torch.tensor([0 if ok else 1], device="cuda")
     dist.all_reduce(flag)
     dist.destroy_process_group()
