@@ -241,6 +241,7 @@ struct BEngine {
     int pend = 0;                     // rows staged in the chunk planes, not yet processed
     CUtensorMap tm_sk_hi, tm_sk_lo, tm_x_hi, tm_x_lo;                 // K2 boxes: l rows x 32 columns
     CUtensorMap tr_t_hi, tr_t_lo, tr_sk_hi, tr_sk_lo, tr_x_hi, tr_x_lo; // K4 boxes
+    CUtensorMap ga_sk_hi, ga_sk_lo, ga_x_hi, ga_x_lo, gb_sk_hi, gb_sk_lo, gb_x_hi, gb_x_lo;   // tiled K2 (l = 256)
     unsigned char* raw = nullptr;     // H2D staging of caller rows: [K][raw_rows][d] of the widest dtype
     size_t raw_bytes = 0;
     long long raw_rows = 0;
@@ -317,10 +318,10 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     MUSED_REQUIRE(ell >= 2 && ell <= BS_MAX_ELL,
                   "schedule=batched supports sketch_dim 2 .. %d (got %lld); use schedule=reference", BS_MAX_ELL, ell);
     MUSED_REQUIRE(d > ell, "schedule=batched needs d > sketch_dim (d=%lld, sketch_dim=%lld)", d, ell);
-    // The kernels run on sketch_dim in {16, 32, 64, 128} and d %% 32 == 0; any other shape is embedded in the
+    // The kernels run on sketch_dim in {16, 32, 64, 128, 256} and d %% 32 == 0; any other shape is embedded in the
     // next such one with zero rows / columns, which changes no Gram entry, eigenvalue or product.
     const long long ell_l = ell, d_l = d;
-    ell = ell_l <= 16 ? 16 : (ell_l <= 32 ? 32 : (ell_l <= 64 ? 64 : 128));
+    ell = ell_l <= 16 ? 16 : (ell_l <= 32 ? 32 : (ell_l <= 64 ? 64 : (ell_l <= 128 ? 128 : 256)));
     d = (d_l + 31) / 32 * 32;
     MUSED_REQUIRE(N >= 1 && beta > 0, "bad N / beta");
     MUSED_REQUIRE(n_levels >= 0 && n_levels <= 64, "n_levels out of range");
@@ -353,7 +354,8 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     // split-K: enough CTAs to cover the SMs, K slices of whole 32-float blocks
     int KS = 16;
     // (sized on ONE stream's instances so that a stream's arithmetic does not depend on how many share the handle)
-    while (KS > 1 && (d % (32 * KS) != 0 || (long long)S1 * KS > 1LL * E->sm_count)) KS >>= 1;
+    const int gram_tiles = ell > 128 ? (int)((2 * ell / GramTiledCfg::TM) * (2 * ell / GramTiledCfg::TN)) : 1;
+    while (KS > 1 && (d % (32 * KS) != 0 || (long long)S1 * KS * gram_tiles > 1LL * E->sm_count)) KS >>= 1;
     if (getenv("MUSED_GRAM_KS")) {
         const int want = atoi(getenv("MUSED_GRAM_KS"));
         if (want >= 1 && want <= 16 && d % (32 * want) == 0) KS = want;
@@ -419,6 +421,25 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
         init[s].skip = 1;
     }
     MUSED_CUDA(cudaMemcpy(D.slots, init.data(), sizeof(BSlot) * Sa, cudaMemcpyHostToDevice));
+    if (ell > 128) {
+        // tiled Gram (n2 = 512): A boxes of 128 rows, B boxes of 256 rows
+        CUresult q[8];
+        const uint64_t xt = (uint64_t)n_streams * (uint64_t)D.xrows;
+        q[0] = encode_tmap_f32_2d(&E->ga_sk_hi, D.skhi, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, 128);
+        q[1] = encode_tmap_f32_2d(&E->ga_sk_lo, D.sklo, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, 128);
+        q[2] = encode_tmap_f32_2d(&E->ga_x_hi, D.xhi, xt, (uint64_t)d, (uint64_t)d, 128);
+        q[3] = encode_tmap_f32_2d(&E->ga_x_lo, D.xlo, xt, (uint64_t)d, (uint64_t)d, 128);
+        q[4] = encode_tmap_f32_2d(&E->gb_sk_hi, D.skhi, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, 256);
+        q[5] = encode_tmap_f32_2d(&E->gb_sk_lo, D.sklo, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, 256);
+        q[6] = encode_tmap_f32_2d(&E->gb_x_hi, D.xhi, xt, (uint64_t)d, (uint64_t)d, 256);
+        q[7] = encode_tmap_f32_2d(&E->gb_x_lo, D.xlo, xt, (uint64_t)d, (uint64_t)d, 256);
+        for (int i = 0; i < 8; ++i)
+            if (q[i] != CUDA_SUCCESS) {
+                set_error("cuTensorMapEncodeTiled failed for the tiled Gram (%d)", (int)q[i]);
+                delete E;
+                return MUSED_ERR_CUDA;
+            }
+    }
     CUresult r1 = encode_tmap_f32_2d(&E->tm_sk_hi, D.skhi, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
     CUresult r2 = encode_tmap_f32_2d(&E->tm_sk_lo, D.sklo, (uint64_t)Sa * 2 * ell, (uint64_t)d, (uint64_t)d, (uint32_t)ell);
     const uint64_t xtot = (uint64_t)n_streams * (uint64_t)D.xrows;
@@ -469,11 +490,39 @@ static int launch_gram(BEngine& E, cudaStream_t st) {
     return 0;
 }
 
+static int launch_gram_tiled(BEngine& E, cudaStream_t st) {
+    using C = GramTiledCfg;
+    MUSED_SMEM_ATTR(k_gram_tiled, C::SMEM_BYTES);
+    GramArgs A;
+    A.slots = E.D.slots;
+    A.Gp = E.D.Gp;
+    A.ell = E.D.ell;
+    A.KS = E.D.KS;
+    A.kblocks = (int)(E.D.d / (32 * E.D.KS));
+    A.x0 = E.D.x0;
+    A.S1 = E.D.S1;
+    A.xrows = (int)E.D.xrows;
+    const int tiles = (E.D.n2 / C::TM) * (E.D.n2 / C::TN);
+    k_gram_tiled<<<dim3(E.D.KS, E.D.S, tiles), 192, C::SMEM_BYTES, st>>>(E.ga_sk_hi, E.ga_sk_lo, E.ga_x_hi, E.ga_x_lo,
+                                                                       E.gb_sk_hi, E.gb_sk_lo, E.gb_x_hi, E.gb_x_lo, A);
+    MUSED_CUDA(cudaGetLastError());
+    return 0;
+}
+
 template <int EPL>
 static int launch_eig(BEngine& E, int n, unsigned long long t_end, cudaStream_t st) {
     static const int mixed = getenv("MUSED_EIG_MIXED") ? atoi(getenv("MUSED_EIG_MIXED")) : 1;   // 0 = float64 sweeps only
     const int smem = (int)ESLayout<EPL>::BYTES;
     MUSED_SMEM_ATTR(k_eig_jacobi<EPL>, smem);
+    if (EPL > 8) {                             // clusters of 16 CTAs are outside the portable limit of 8
+        static std::atomic<unsigned long long> np_done{0ull};
+        int dev = 0;
+        MUSED_CUDA(cudaGetDevice(&dev));
+        if (!((np_done.load() >> (dev & 63)) & 1ull)) {
+            MUSED_CUDA(cudaFuncSetAttribute(k_eig_jacobi<EPL>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+            np_done.fetch_or(1ull << (dev & 63));
+        }
+    }
     EigArgs A;
     A.slots = E.D.slots;
     A.G = E.D.G;
@@ -531,7 +580,8 @@ int bengine_chunk_gram(BEngine* Ep, cudaStream_t st) {
         case 16: rc = launch_gram<32>(E, st); break;
         case 32: rc = launch_gram<64>(E, st); break;
         case 64: rc = launch_gram<128>(E, st); break;
-        default: rc = launch_gram<256>(E, st); break;
+        case 128: rc = launch_gram<256>(E, st); break;
+        default: rc = launch_gram_tiled(E, st); break;
     }
     if (rc) return rc;
     k_gram_reduce<<<std::min<long long>(((long long)D.S * D.n2 * D.n2 + 255) / 256, 8ll * E.sm_count), 256, 0, st>>>(D);
@@ -554,13 +604,14 @@ int bengine_chunk_finish(BEngine* Ep, cudaStream_t st) {
             case 16: rc = launch_eig<1>(E, n, t_end, st); break;
             case 32: rc = launch_eig<2>(E, n, t_end, st); break;
             case 64: rc = launch_eig<4>(E, n, t_end, st); break;
-            default: rc = launch_eig<8>(E, n, t_end, st); break;
+            case 128: rc = launch_eig<8>(E, n, t_end, st); break;
+            default: rc = launch_eig<16>(E, n, t_end, st); break;
         }
         if (rc) return rc;
         E.mark(3, st);
         E.mark(4, st);
         MUSED_SMEM_ATTR(k_rotate_tc, RotCfg::SMEM_BYTES);
-        k_rotate_tc<<<dim3((unsigned)((D.d + RotCfg::NT - 1) / RotCfg::NT), (unsigned)D.S), 192, RotCfg::SMEM_BYTES, st>>>(
+        k_rotate_tc<<<dim3((unsigned)((D.d + RotCfg::NT - 1) / RotCfg::NT), (unsigned)D.S, (unsigned)std::max(1, D.ell / 128)), 192, RotCfg::SMEM_BYTES, st>>>(
             E.tr_t_hi, E.tr_t_lo, E.tr_sk_hi, E.tr_sk_lo, E.tr_x_hi, E.tr_x_lo, D);
         MUSED_CUDA(cudaGetLastError());
         E.mark(4, st);

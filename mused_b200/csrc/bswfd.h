@@ -6,7 +6,7 @@
 
 namespace mused {
 
-constexpr int BS_MAX_ELL = 128;
+constexpr int BS_MAX_ELL = 256;
 
 struct BDev {
     int S, ell, n2, capn, KS;  // S = FD instances of ALL streams; ell = PHYSICAL sketch rows (16 / 32 / 64 / 128), n2 = 2 ell

@@ -53,8 +53,9 @@ k_rotate_tc(const __grid_constant__ CUtensorMap tm_t_hi, const __grid_constant__
                 make_float4(h.x + l.x, h.y + l.y, h.z + l.z, h.w + l.w);
         }
     };
+    const int mt = blockIdx.z;                        // rows [128 mt, +128) of the new sketch (l > 128: l / 128 CTAs per tile)
     if (sl.skip) {
-        if (nraw > 0) raw_copy(threadIdx.x >> 5, 6);
+        if (nraw > 0 && mt == 0) raw_copy(threadIdx.x >> 5, 6);
         return;
     }
     extern __shared__ unsigned char smem_dyn[];
@@ -95,7 +96,7 @@ k_rotate_tc(const __grid_constant__ CUtensorMap tm_t_hi, const __grid_constant__
     if (warp == 0) {
         if (lane == 0) {
             const int t_rows = ell < 128 ? ell : 128;                 // rows of one T box
-            const int row_t = s * ell;
+            const int row_t = s * ell + 128 * mt;
             const int row_sk = (s * 2 + src) * ell;
             for (int kb = 0; kb < kblocks; ++kb) {
                 const int st = kb % C::NST;
@@ -150,10 +151,10 @@ k_rotate_tc(const __grid_constant__ CUtensorMap tm_t_hi, const __grid_constant__
         }
     } else {
         const int q = warp & 3;
-        if (nraw > 0) raw_copy(warp - 2, 4);             // under the TMA / MMA pipeline of warps 0 and 1
+        if (nraw > 0 && mt == 0) raw_copy(warp - 2, 4);  // under the TMA / MMA pipeline of warps 0 and 1
         umma::mbar_wait(accum, 0);
         umma::tc_fence_after();
-        const int r = q * 32 + lane;
+        const int r = 128 * mt + q * 32 + lane;
         const long long d = D.d;
         int ds = -1;
         if (r < ell) ds = D.dump_slot[(size_t)s * ell + r];

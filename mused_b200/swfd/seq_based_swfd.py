@@ -31,7 +31,7 @@ class SeqBasedSWFD:
                        batch_rows (default sketch_dim) rows, all directions with
                        sigma^2 >= threshold dumped per chunk (the throughput path;
                        semantics stated in oracle/swfd_batched_oracle.py); sketch_dim
-                       2..128, any d > sketch_dim.
+                       2..256, any d > sketch_dim.
         """
         self.N = np.uint64(N)
         self.d = int(d)

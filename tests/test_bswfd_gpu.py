@@ -35,7 +35,8 @@ def _check_query(gpu, ora, Aw):
     assert np.max(np.abs(a[big] - b[big]) / a[big]) <= SIG_RTOL
     assert np.max(np.abs(a[~big] - b[~big]), initial=0.0) <= 1e-5 * a.max()
     eg, eo = so.cov_error(Aw, sg), so.cov_error(Aw, so_)
-    assert abs(eg - eo) <= COV_RTOL * eo, (eg, eo)
+    # l = 256: the rotate contracts 512 fp32-accumulated terms per entry and the error itself is ~4x smaller
+    assert abs(eg - eo) <= (COV_RTOL if gpu.sketch_dim <= 128 else 3e-4) * eo, (eg, eo)
     assert eg <= 4.0 / gpu.sketch_dim                      # DS-FD bound (test_bibd.py:80-81)
     assert gpu.get_size() == ora.get_size()
     nz = s2g > 1e-9 * s2g.max()
@@ -45,7 +46,8 @@ def _check_query(gpu, ora, Aw):
         assert (g["n_flush"], g["n_dump"], g["n_raw"]) == (o["n_flush"], o["n_dump"], o["n_raw"])
         assert g["last_dump_time"] == o["last_dump_time"]
         assert abs(g["delta"] - o["delta"]) <= 1e-4 * o["delta"] + 1e-12
-        np.testing.assert_allclose(np.sort(g["s2"]), np.sort(o["s2"]), atol=5e-5 * max(o["s2"].max(), 1e-30))
+        np.testing.assert_allclose(np.sort(g["s2"]), np.sort(o["s2"]),
+                                   atol=(5e-5 if gpu.sketch_dim <= 128 else 1.5e-4) * max(o["s2"].max(), 1e-30))
     return eg, eo
 
 
@@ -59,6 +61,9 @@ def _check_query(gpu, ora, Aw):
     (24, 100, 400, 1200, 1.0),         # neither l nor d a kernel shape
     (100, 1000, 1500, 3200, 2.0),
     (3, 40, 200, 700, 1.0),
+    (256, 1024, 3000, 6200, 2.0),      # l = 256: tiled tcgen05 Gram (n2 = 512), 16-CTA eigensolve clusters, 2 row tiles in the rotate
+    (200, 800, 2500, 5200, 2.0),       # padded to l = 256 inside
+    (256, 4096, 4000, 4600, 2.0),      # BASELINE configs[3] shape (d=4096, l=256), shortened
 ])
 def test_batched_engine_matches_batched_oracle(ell, d, N, n, scale):
     from mused_b200.swfd import SeqBasedSWFD
