@@ -4,12 +4,14 @@ Same steps, same order, same arguments as ``process_streaming_data(approach="SWF
 per full window -- one kNN adjacency per modality (create_adjacency_matrix, :44-49), OR-fusion
 (:56), the rows of the fused W x W matrix through the sliding-window FD sketch (:60-67), ``get()``
 and the transpose fix-up (:70-76), KMeans (:97), Hungarian matching with the previous window
-(:106-110).  String modalities (username / tags / text) are host-side string processing in the
+(:106-110).  The fused adjacency stays on the device as one uint8 matrix from the top-k kernels to the sketch's
+row staging kernel (no per-modality W x W float64 matrices, no host round trip).  String modalities (username / tags / text) are host-side string processing in the
 reference and are not taken here.
 """
 from __future__ import annotations
 
 import numpy as np
+import torch
 
 from . import matrix_operations as mo
 from .swfd import SeqBasedSWFD
@@ -31,15 +33,15 @@ def process_streaming_data(data_modalities, modality_types, complete_true_labels
             true_labels = np.asarray(complete_true_labels[lo:i + 1])
             all_true.extend(true_labels)
             n_clusters = len(np.unique(true_labels))                                          # main.py:41
-            mats = [mo.create_adjacency_matrix(np.asarray(m[lo:i + 1]), t, k_basis=k_basis, device=device)
-                    for m, t in zip(data_modalities, modality_types)]                         # main.py:44-49
-            fused = mo.fuse_matrices(mats)                                                    # main.py:56
+            # main.py:44-56: one uint8 W x W matrix on the device, every modality's top-k kernel ORs into it
+            fused = mo.fused_adjacency([np.asarray(m[lo:i + 1]) for m in data_modalities], modality_types,
+                                       k_basis=k_basis, device=device)
             if swfd is None:                                                                  # main.py:60-62
-                max_norm = float(np.max(np.linalg.norm(fused, axis=1) ** 2))
+                max_norm = float(fused.sum(dim=1, dtype=torch.int64).max().item())            # ||0/1 row||^2 = degree
                 swfd = SeqBasedSWFD(N=window_size, R=max_norm, d=fused.shape[1], sketch_dim=reduced_dim,
                                     schedule=schedule,
                                     device=int(str(device).split(":")[-1]) if ":" in str(device) else 0)
-            swfd.fit(fused)                                   # main.py:65-67, the W rows in one call
+            swfd.fit(fused)                                   # main.py:65-67, the W uint8 rows in one call, device-resident
             red = swfd.get()[0]                               # main.py:70
             red = np.asarray(red.cpu() if hasattr(red, "cpu") else red)
             if red.shape[0] != window_size:                   # main.py:73-76

@@ -61,9 +61,9 @@ def _check_query(gpu, ora, Aw):
     (24, 100, 400, 1200, 1.0),         # neither l nor d a kernel shape
     (100, 1000, 1500, 3200, 2.0),
     (3, 40, 200, 700, 1.0),
-    (256, 1024, 3000, 6200, 2.0),      # l = 256: tiled tcgen05 Gram (n2 = 512), 16-CTA eigensolve clusters, 2 row tiles in the rotate
-    (200, 800, 2500, 5200, 2.0),       # padded to l = 256 inside
-    (256, 4096, 4000, 4600, 2.0),      # BASELINE configs[3] shape (d=4096, l=256), shortened
+    (256, 1024, 2000, 4200, 2.0),      # l = 256: tiled tcgen05 Gram (n2 = 512), 16-CTA eigensolve clusters, 2 row tiles in the rotate
+    (200, 800, 1500, 3200, 2.0),       # padded to l = 256 inside
+    (256, 4096, 2000, 2600, 2.0),      # BASELINE configs[3] shape (d=4096, l=256), shortened
 ])
 def test_batched_engine_matches_batched_oracle(ell, d, N, n, scale):
     from mused_b200.swfd import SeqBasedSWFD
@@ -143,7 +143,7 @@ def test_batched_engine_adjacency_rows_and_cov_error_vs_reference_schedule():
 def test_batched_engine_rejects_unsupported_shapes():
     from mused_b200.swfd import SeqBasedSWFD
     with pytest.raises(ValueError):
-        SeqBasedSWFD(100, 8.0, 1024, 200, schedule="batched")   # sketch_dim > 128
+        SeqBasedSWFD(100, 8.0, 1024, 300, schedule="batched")   # sketch_dim > 256
     with pytest.raises(ValueError):
         SeqBasedSWFD(100, 8.0, 16, 16, schedule="batched")      # d <= sketch_dim
     with pytest.raises(ValueError):

@@ -159,3 +159,29 @@ def test_oracle_reproduces_full_length_reference_fixture_prefix(golden_dir):
         assert np.array_equal(s2, g["sigma2"][qi]) and delta == g["delta"][qi]
         err = so.cov_error(A64[qi * 2000:(qi + 1) * 2000], B)       # BLAS thread count changes the last bits
         assert abs(err - g["cov_err"][qi]) <= 1e-10 * g["cov_err"][qi]
+
+
+@pytest.mark.skipif(not ref_shim.available(), reason="reference tree not present (GPU box)")
+def test_knn_adjacency_oracle_vs_reference_text_branch():
+    """The reference's only cosine code path: TF-IDF -> cosine_similarity -> argsort top-(k_basis+1) -> writer
+    (matrix_operations.py:91-110, :123-130) on a toy corpus, against the cosine branch of the adjacency oracle
+    fed the same TF-IDF vectors."""
+    from sklearn.feature_extraction.text import TfidfVectorizer
+    swfd, mo, me = ref_shim.load()
+    rng = np.random.default_rng(3)
+    vocab = ["concert", "stage", "crowd", "band", "lights", "march", "protest", "street", "flags", "police",
+             "soccer", "goal", "stadium", "fans", "match", "beach", "sunset", "waves", "sand", "boat"]
+    rows = []
+    for i in range(36):
+        topic = (i // 9) * 5
+        words = [vocab[topic + int(w)] for w in rng.integers(0, 5, size=4)] + [vocab[int(w)] for w in rng.integers(0, 20, size=2)]
+        title, desc = " ".join(words[:3]), " ".join(words[3:])
+        rows.append([title, desc if i % 7 else ""])          # some blank descriptions (:100)
+    data = np.array(rows, dtype=object).astype(str)
+    ref = mo.create_adjacency_matrix(data, "text", k_basis=4)       # k = 5
+    text = np.where(data[:, 0] != "", data[:, 0], " ") + " " + np.where(data[:, 1] != "", data[:, 1], " ")
+    V = TfidfVectorizer().fit_transform(text).toarray()
+    adj, margin = ops_oracle.knn_adjacency(V, 5, "cosine")
+    clear = margin > 1e-9                                       # rows whose 5th / 6th neighbours are not tied
+    assert clear.sum() >= 20
+    assert np.array_equal(ref[clear].astype(np.uint8), adj[clear])

@@ -15,8 +15,9 @@ for r in rows[1:]:
 allns = sum(tot.values())
 ref = sum(v for k, v in tot.items() if "k_swfd_rows" in k or "k_stage_rows" in k or "k_gather_stack" in k)
 with open(dst, "w") as o:
-    o.write("# ncu --metrics gpu__time_duration.sum --clock-control none, python bench.py --steps 1 --warmup 1\n")
-    o.write("# the run contains the device leg, the e2e leg and the reference-schedule leg (k_swfd_rows);\n")
+    o.write("# ncu --metrics gpu__time_duration.sum --clock-control none, the bench command of tools/ncu_capture.sh\n")
+    o.write("# (python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e --streams= --no-sharded --no-refsched): 4 windows of the\n")
+    o.write("# batched device leg + the same-window cov-error check on the fixture stream (one strict run: k_swfd_rows);\n")
     o.write("# share_batched = share of the batched-schedule kernels only\n")
     o.write("kernel,launches,total_ns,share_all,share_batched,max_ns\n")
     for k, v in tot.most_common():
