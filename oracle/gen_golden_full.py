@@ -55,6 +55,10 @@ def config(name, rows=None):
         A = synth.lowrank_stream(n, 1024, seed=0)
         assert synth.row_norm2_max(A) <= 64.0
         return dict(A=A, labels=None, centres=None, N=10000, ell=128, qstep=2500, R=64.0, tau=None)
+    if name in ("l256", "l512"):   # strict engine beyond sketch_dim 128 (configs[3] / configs[4] sketch sizes, small d)
+        n, d, seed, N, ell = (2000, 640, 7, 1500, 256) if name == "l256" else (1500, 768, 8, 1200, 512)
+        A = synth.lowrank_stream(rows or n, d, seed=seed, scale=2.0)
+        return dict(A=A, labels=None, centres=None, N=N, ell=ell, qstep=500, R=synth.row_norm2_max(A), tau=None)
     raise SystemExit("unknown config " + name)
 
 
@@ -81,7 +85,7 @@ def summarise(B, s2, delta, size, level, A_w, P):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("config", choices=["c0", "c1"])
+    ap.add_argument("config", choices=["c0", "c1", "l256", "l512"])
     ap.add_argument("--rows", type=int, default=0)
     ap.add_argument("--no-oracle", action="store_true")
     args = ap.parse_args()

@@ -249,8 +249,9 @@ def test_multi_stream_engine_equals_solo_runs(shape):
             ms.fit(A[:, a:b])                        # host rows
         for k in range(K):
             solos[k].fit(Ad[k, a:b])
+        # sizes first: a get() closes the open chunk of EVERY stream of the handle (they advance in lock-step)
+        assert [ms.get_size(k) for k in range(K)] == [solos[k].get_size() for k in range(K)]
         for k in range(K):
-            assert ms.get_size(k) == solos[k].get_size()
             Bm, s2m, vtm, dm = ms.get(k)
             lm = ms.last_level
             Bs, s2s, vts, ds = solos[k].get()

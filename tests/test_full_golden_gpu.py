@@ -35,6 +35,9 @@ def _stream(g):
     from mused_b200 import synth
     if str(g["config"]) == "c0":
         A, labels, centres = synth.event_stream(int(g["n"]), blocks=(256, 192, 32, 32), n_events=150, seed=0)
+    elif str(g["config"]) in ("l256", "l512"):
+        A = synth.lowrank_stream(int(g["n"]), int(g["d"]), seed=7 if str(g["config"]) == "l256" else 8, scale=2.0)
+        labels, centres = None, None
     else:
         A, labels, centres = synth.lowrank_stream(int(g["n"]), int(g["d"]), seed=0), None, None
     assert hashlib.sha256(np.ascontiguousarray(A).tobytes()).hexdigest() == str(g["sha_A"]), \
@@ -53,7 +56,7 @@ def _load(golden_dir, name):
     return np.load(p)
 
 
-@pytest.mark.parametrize("name", ["c0", "c1"])
+@pytest.mark.parametrize("name", ["c0", "c1", "l256", "l512"])
 def test_reference_schedule_full_length(golden_dir, name):
     from mused_b200.swfd import SeqBasedSWFD
     g = _load(golden_dir, name)
