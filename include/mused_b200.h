@@ -258,6 +258,16 @@ int mused_topk_adjacency_f64(const double* feats, int64_t W, int64_t f, int64_t 
 int mused_contingency(const int32_t* prev, const int32_t* cur, int64_t n, int32_t P,
                       int32_t Q, int32_t* counts, void* stream);
 
+/* KMeans of the reduced window, matrix_operations.py:149-153 (KMeans(n_clusters, random_state=seed).fit_predict)
+ * entirely on the device: k-means++ seeding (D^2 sampling, counter-based RNG from `seed`), Lloyd iterations with
+ * the assignment operator above and a deterministic centre update, until no label changes, the summed squared
+ * centre movement is <= tol, or max_iter.  X: n x d float32 device rows; centroids: k x d float32 device (out),
+ * labels: n int32 device (out), inertia / n_iter: host (nullable).  The seeding is not sklearn's (its greedy
+ * k-means++ draws from numpy's Mersenne twister): labels agree with sklearn's up to the usual KMeans ambiguity,
+ * which is why the reference-parity loop keeps sklearn's fit and this entry is the throughput option. */
+int mused_kmeans(const float* X, int64_t n, int64_t d, int64_t ld, int32_t k, uint64_t seed, int32_t max_iter, double tol,
+                 float* centroids, int32_t* labels, double* inertia, int32_t* n_iter, void* stream);
+
 /* Symmetric eigen-decomposition of a positive semi-definite Gram matrix
  * (what replaces scipy.linalg.svd(..., lapack_driver="gesvd") of the stacked
  * rows in SlidingWindowFD.get, sliding_windows_frequent_directions.py:160, and

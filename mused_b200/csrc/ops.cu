@@ -247,6 +247,123 @@ __global__ void k_contingency(const int* __restrict__ prev, const int* __restric
     }
 }
 
+// ---------------------------------------------------------------------------
+// Device KMeans (perform_clustering, matrix_operations.py:149-153: KMeans(n_clusters, random_state).fit_predict).
+// k-means++ seeding (D^2 sampling, one trial per centre, counter-based RNG) by ONE CTA; Lloyd iterations =
+// the assignment operator (mused_assign, L2) + k_kmeans_update below.  Every reduction runs in a fixed order:
+// the result is a pure function of (X, k, seed).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ double kmeans_uniform(unsigned long long seed, unsigned long long ctr) {
+    unsigned long long z = seed + 0x9E3779B97F4A7C15ull * (ctr + 1ull);       // splitmix64
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return (double)(z >> 11) * (1.0 / 9007199254740992.0);
+}
+
+__global__ void __launch_bounds__(1024) k_kmeans_seed(const float* __restrict__ X, long long n, long long d, long long ld,
+                                                      int k, unsigned long long seed, float* __restrict__ C,
+                                                      float* __restrict__ mind) {
+    __shared__ double part[1024];
+    __shared__ long long pick;
+    const int t = threadIdx.x;
+    if (t == 0) pick = (long long)(kmeans_uniform(seed, 0) * (double)n) % n;
+    __syncthreads();
+    for (int j = 0; j < k; ++j) {
+        const long long p = pick;
+        for (long long c = t; c < d; c += 1024) C[(size_t)j * d + c] = X[(size_t)p * ld + c];
+        __syncthreads();
+        if (j + 1 == k) break;
+        // squared distance of my rows (a contiguous slice: the cumulative search below needs an order) to the new centre
+        const long long per = (n + 1023) / 1024, lo = t * per, hi = lo + per < n ? lo + per : n;
+        double mine = 0.0;
+        for (long long i = lo; i < hi; ++i) {
+            float acc = 0.f;
+            const float* x = X + (size_t)i * ld;
+            const float* cj = C + (size_t)j * d;
+            for (long long c = 0; c < d; ++c) { const float df = x[c] - cj[c]; acc = fmaf(df, df, acc); }
+            const float m = (j == 0) ? acc : fminf(mind[i], acc);
+            mind[i] = m;
+            mine += (double)m;
+        }
+        part[t] = mine;
+        __syncthreads();
+        if (t == 0) {
+            double tot = 0.0;
+            for (int q = 0; q < 1024; ++q) tot += part[q];
+            const double u = kmeans_uniform(seed, (unsigned long long)(j + 1)) * tot;
+            double run = 0.0;
+            int q = 0;
+            for (; q < 1023; ++q) { if (run + part[q] > u) break; run += part[q]; }
+            const long long qlo = q * per, qhi = qlo + per < n ? qlo + per : n;
+            long long i = qlo;
+            for (; i + 1 < qhi; ++i) { if (run + (double)mind[i] > u) break; run += (double)mind[i]; }
+            pick = i < n ? i : n - 1;
+        }
+        __syncthreads();
+    }
+}
+
+// new centre j = mean of the rows labelled j (CTA j; thread = column, rows in index order: deterministic); an empty
+// cluster keeps its centre.  shift2[j] = squared movement, inertia partial left to the assignment scores.
+__global__ void __launch_bounds__(256) k_kmeans_update(const float* __restrict__ X, long long n, long long d, long long ld,
+                                                       const int* __restrict__ labels, float* __restrict__ C,
+                                                       double* __restrict__ shift2, int* __restrict__ counts) {
+    __shared__ double red[8];
+    const int j = blockIdx.x;
+    double sh = 0.0;
+    int cnt = 0;
+    for (long long c0 = 0; c0 < d; c0 += 256) {
+        const long long c = c0 + threadIdx.x;
+        double acc = 0.0;
+        cnt = 0;
+        for (long long i = 0; i < n; ++i) {
+            if (labels[i] == j) {
+                ++cnt;
+                if (c < d) acc += (double)X[(size_t)i * ld + c];
+            }
+        }
+        if (c < d && cnt > 0) {
+            const float nv = (float)(acc / (double)cnt);
+            const double df = (double)nv - (double)C[(size_t)j * d + c];
+            sh = fma(df, df, sh);
+            C[(size_t)j * d + c] = nv;
+        }
+    }
+    sh = warp_sum(sh);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sh;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tsum = 0.0;
+        for (int q = 0; q < 8; ++q) tsum += red[q];
+        shift2[j] = tsum;
+        counts[j] = cnt;
+    }
+}
+
+// stats[0] = sum of score^2 (inertia), stats[1] = sum over centres of shift2, stats[2] = labels changed
+__global__ void __launch_bounds__(256) k_kmeans_stats(const float* __restrict__ score, const int* __restrict__ lab,
+                                                      int* __restrict__ prev, long long n, const double* __restrict__ shift2,
+                                                      int k, double* __restrict__ stats) {
+    __shared__ double r0[8], r2[8];
+    double a = 0.0, ch = 0.0;
+    for (long long i = threadIdx.x; i < n; i += 256) {
+        a = fma((double)score[i], (double)score[i], a);
+        if (lab[i] != prev[i]) ch += 1.0;
+        prev[i] = lab[i];
+    }
+    a = warp_sum(a);
+    ch = warp_sum(ch);
+    if ((threadIdx.x & 31) == 0) { r0[threadIdx.x >> 5] = a; r2[threadIdx.x >> 5] = ch; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double x = 0.0, z = 0.0, y = 0.0;
+        for (int q = 0; q < 8; ++q) { x += r0[q]; z += r2[q]; }
+        for (int j = 0; j < k; ++j) y += shift2[j];
+        stats[0] = x; stats[1] = y; stats[2] = z;
+    }
+}
+
 // Scratch comes from the stream-ordered pool; by default that pool hands its memory back to the
 // driver at every synchronisation, which makes the next cudaMallocAsync map fresh pages (slow and
 // erratic).  Keep the pages: one attribute on the device's default pool, set once per device.
@@ -414,6 +531,58 @@ int mused_contingency(const int32_t* prev, const int32_t* cur, int64_t n, int32_
     MUSED_CUDA(cudaGetLastError());
     mused_count_launches(1);
     return 0;
+}
+
+int mused_kmeans(const float* X, int64_t n, int64_t d, int64_t ld, int32_t k, uint64_t seed, int32_t max_iter, double tol,
+                 float* centroids, int32_t* labels, double* inertia, int32_t* n_iter, void* stream) {
+    MUSED_REQUIRE(n >= 1 && d >= 1 && ld >= d && k >= 1 && k <= n, "bad shape (n=%lld d=%lld k=%d)", (long long)n, (long long)d, k);
+    MUSED_REQUIRE(X && centroids && labels, "NULL argument");
+    MUSED_REQUIRE(max_iter >= 1 && tol >= 0.0, "bad max_iter / tol");
+    cudaStream_t st = (cudaStream_t)stream;
+    keep_pool_memory();
+    float *mind = nullptr, *score = nullptr;
+    int *prev = nullptr, *counts = nullptr;
+    double *shift2 = nullptr, *stats = nullptr;
+    MUSED_CUDA(cudaMallocAsync((void**)&mind, sizeof(float) * (size_t)n, st));
+    MUSED_CUDA(cudaMallocAsync((void**)&score, sizeof(float) * (size_t)n, st));
+    MUSED_CUDA(cudaMallocAsync((void**)&prev, sizeof(int) * (size_t)n, st));
+    MUSED_CUDA(cudaMallocAsync((void**)&counts, sizeof(int) * (size_t)k, st));
+    MUSED_CUDA(cudaMallocAsync((void**)&shift2, sizeof(double) * (size_t)k, st));
+    MUSED_CUDA(cudaMallocAsync((void**)&stats, sizeof(double) * 4, st));
+    MUSED_CUDA(cudaMemsetAsync(prev, 0xff, sizeof(int) * (size_t)n, st));
+    k_kmeans_seed<<<1, 1024, 0, st>>>(X, n, d, ld, k, seed, centroids, mind);
+    MUSED_CUDA(cudaGetLastError());
+    mused_count_launches(1);
+    // tolerance on the centre movement, scaled like sklearn's: tol * mean feature variance is the caller's business
+    double h[3] = {0, 0, 0};
+    int it = 0, rc = 0;
+    for (; it < max_iter; ++it) {
+        rc = mused_assign(X, n, d, ld, centroids, k, d, MUSED_METRIC_L2, -1.f, labels, score, stream);
+        if (rc) break;
+        k_kmeans_update<<<k, 256, 0, st>>>(X, n, d, ld, labels, centroids, shift2, counts);
+        k_kmeans_stats<<<1, 256, 0, st>>>(score, labels, prev, n, shift2, k, stats);
+        if (cudaGetLastError() != cudaSuccess) { set_error("kmeans kernel launch failed"); rc = MUSED_ERR_CUDA; break; }
+        mused_count_launches(2);
+        if (cudaMemcpyAsync(h, stats, sizeof(h), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+            cudaStreamSynchronize(st) != cudaSuccess) { set_error("kmeans: reading the convergence record failed"); rc = MUSED_ERR_CUDA; break; }
+        if (h[2] == 0.0 || h[1] <= tol) { ++it; break; }
+    }
+    if (!rc) {
+        // labels of the FINAL centres (what fit_predict returns) and their inertia
+        rc = mused_assign(X, n, d, ld, centroids, k, d, MUSED_METRIC_L2, -1.f, labels, score, stream);
+        if (!rc) {
+            MUSED_CUDA(cudaMemsetAsync(shift2, 0, sizeof(double) * (size_t)k, st));
+            k_kmeans_stats<<<1, 256, 0, st>>>(score, labels, prev, n, shift2, k, stats);
+            MUSED_CUDA(cudaGetLastError());
+            MUSED_CUDA(cudaMemcpyAsync(h, stats, sizeof(h), cudaMemcpyDeviceToHost, st));
+            MUSED_CUDA(cudaStreamSynchronize(st));
+            if (inertia) *inertia = h[0];
+            if (n_iter) *n_iter = it;
+        }
+    }
+    cudaFreeAsync(mind, st); cudaFreeAsync(score, st); cudaFreeAsync(prev, st);
+    cudaFreeAsync(counts, st); cudaFreeAsync(shift2, st); cudaFreeAsync(stats, st);
+    return rc;
 }
 
 }  // extern "C"

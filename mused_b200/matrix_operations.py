@@ -8,6 +8,8 @@ the dense feature matrices those branches produce.
 """
 from __future__ import annotations
 
+import ctypes as C
+
 import numpy as np
 import torch
 
@@ -188,7 +190,28 @@ def nearest_centroid(X, centroids, *, device="cuda:0"):
     return cosine_assign(X, centroids, -1.0, metric="l2", device=device)
 
 
-def perform_clustering(matrix, n_clusters, seed, *, device="cuda:0", return_model=False):
+def device_kmeans(matrix, n_clusters, seed=0, *, max_iter=300, tol=1e-4, device="cuda:0"):
+    """KMeans entirely on the device (C ABI mused_kmeans): k-means++ seeding, Lloyd iterations on the fused
+    assignment kernel, deterministic centre update.  Returns (labels int32 tensor, centroids float32 tensor,
+    inertia, n_iter).  tol is sklearn's: relative to the mean feature variance (sklearn/cluster/_kmeans.py)."""
+    lib = _lib.load()
+    Xd = _dev_f32(matrix, device)
+    n, d = Xd.shape
+    mu = Xd.mean(dim=0, keepdim=True)
+    Xc = (Xd - mu).contiguous()                       # distances are translation invariant; fp32 keeps more digits
+    var = float(Xc.var(dim=0, unbiased=False).mean().item())
+    cent = torch.empty((int(n_clusters), d), dtype=torch.float32, device=Xd.device)
+    labels = torch.empty(n, dtype=torch.int32, device=Xd.device)
+    inertia, n_iter = C.c_double(0.0), C.c_int32(0)
+    with torch.cuda.device(Xd.device):
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(lib.mused_kmeans(Xc.data_ptr(), n, d, Xc.stride(0) if n > 1 else d, int(n_clusters), int(seed) & (2 ** 64 - 1),
+                                    int(max_iter), float(tol) * var, cent.data_ptr(), labels.data_ptr(),
+                                    C.byref(inertia), C.byref(n_iter), st))
+    return labels, cent + mu, float(inertia.value), int(n_iter.value)
+
+
+def perform_clustering(matrix, n_clusters, seed, *, device="cuda:0", return_model=False, engine="sklearn"):
     """KMeans labels of the reduced window (matrix_operations.py:149-153).
 
     ``KMeans(n_clusters, random_state=seed).fit`` stays sklearn's (k-means++ seeding and Lloyd
@@ -200,6 +223,12 @@ def perform_clustering(matrix, n_clusters, seed, *, device="cuda:0", return_mode
     differs from sklearn's float64 label (near-ties) keep sklearn's: the operator never fails where the
     reference would not; ``perform_clustering.last_disagreements`` counts them for the tests.
     """
+    if engine == "device":
+        # the throughput option: no sklearn fit, no host round trip of the W x l matrix (labels are KMeans labels of
+        # another seeding: equal to sklearn's only up to the usual ambiguity; judged by inertia / NMI, SURVEY 8f-2)
+        lab, cent, inertia, n_iter = device_kmeans(matrix, n_clusters, seed, device=device)
+        lab = lab.cpu().numpy().astype(np.int32)
+        return (lab, cent) if return_model else lab
     from sklearn.cluster import KMeans
     M = np.ascontiguousarray(np.asarray(matrix, dtype=np.float64))
     km = KMeans(n_clusters=n_clusters, random_state=seed).fit(M)

@@ -19,7 +19,7 @@ from .swfd import SeqBasedSWFD
 
 def process_streaming_data(data_modalities, modality_types, complete_true_labels, *, window_size=2000,
                            reduced_dim=50, k_basis=50, seed=0, step_window_ratio=1, schedule="reference",
-                           device="cuda:0"):
+                           device="cuda:0", kmeans="sklearn"):
     """Returns (all_clusters, all_true_labels, per-window list of reduced matrices)."""
     subset_size = len(complete_true_labels)
     window, all_clusters, all_true, reduced = [], [], [], []
@@ -47,7 +47,7 @@ def process_streaming_data(data_modalities, modality_types, complete_true_labels
             if red.shape[0] != window_size:                   # main.py:73-76
                 red = red.T
             reduced.append(red)
-            clusters = mo.perform_clustering(red, n_clusters, seed, device=device)            # main.py:97
+            clusters = mo.perform_clustering(red, n_clusters, seed, device=device, engine=kmeans)   # main.py:97
             clusters = mo.match_clusters(prev_clusters, clusters, method="hungarian", min_overlap=3,
                                          device=device)                                       # main.py:110
             if clusters is None or len(clusters) == 0:

@@ -4,7 +4,7 @@ expiry, full level ladder) against fixtures produced by the UNMODIFIED reference
 (oracle/gen_golden_full.py -> tests/golden/full_c0.npz, full_c1.npz).
 
   * schedule="reference": north_star's bars are singular values within 1e-4 relative and covariance error
-    within 1e-3 relative; asserted here at 1e-7 (sigma >= 0.05 sigma_max; 1e-4 down to 1e-3 sigma_max) / 1e-6, plus identical get_size(), chosen level, delta,
+    within 1e-3 relative; asserted here at 1e-6 (sigma >= 0.05 sigma_max; 1e-4 down to 1e-3 sigma_max) / 1e-6, plus identical get_size(), chosen level, delta,
     snapshot (s, t) lists and final sigma^2 of every FD instance.
   * schedule="batched" (the throughput path): its decisions differ from the reference's by construction, so
     what is asserted is its covariance error ON THE SAME WINDOWS next to the reference's: never above the
@@ -27,7 +27,7 @@ from oracle import swfd_oracle as so
 
 pytestmark = pytest.mark.gpu
 
-SIG_RTOL = 1e-7          # north_star allows 1e-4
+SIG_RTOL = 1e-6          # north_star allows 1e-4 (measured: 1.4e-7 at sigma = 0.06 sigma_max after 10 000 rows)
 COV_RTOL = 1e-6          # north_star allows 1e-3
 
 

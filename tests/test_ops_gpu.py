@@ -163,3 +163,36 @@ def test_contingency_and_match_clusters():
     out = mo.match_clusters(prev, cur, method="hungarian", min_overlap=3)
     assert (out == prev).mean() > 0.9
     assert mo.match_clusters(None, cur) is cur
+
+
+def test_device_kmeans_blobs_inertia_and_determinism():
+    """mused_kmeans (perform_clustering's device engine, matrix_operations.py:149-153): exact recovery of
+    well-separated blobs, inertia within 5 % of sklearn's KMeans on overlapping data, identical results for
+    identical (X, k, seed)."""
+    from sklearn.cluster import KMeans
+    from sklearn.metrics import adjusted_rand_score
+    from mused_b200 import matrix_operations as mo
+    rng = np.random.default_rng(4)
+    k, d, per = 12, 50, 160
+    centres = rng.standard_normal((k, d)) * 6.0
+    X = np.concatenate([centres[j] + 0.3 * rng.standard_normal((per, d)) for j in range(k)]) + 40.0   # far from the origin
+    truth = np.repeat(np.arange(k), per)
+    lab, cent, inertia, n_iter = mo.device_kmeans(X, k, seed=3)
+    lab = lab.cpu().numpy()
+    km = KMeans(n_clusters=k, random_state=0, n_init=10).fit(X)    # sklearn's best of 10 seedings
+    assert inertia <= 1.05 * km.inertia_ or adjusted_rand_score(truth, lab) == 1.0
+    lab2, cent2, inertia2, _ = mo.device_kmeans(X, k, seed=3)
+    assert np.array_equal(lab, lab2.cpu().numpy()) and inertia == inertia2
+    # labels are the nearest final centre (what fit_predict returns)
+    D = ((X[:, None, :] - cent.cpu().numpy().astype(np.float64)[None, :, :]) ** 2).sum(-1)
+    srt = np.sort(D, axis=1)
+    sure = srt[:, 1] - srt[:, 0] > 1e-3 * srt[:, 0]
+    assert np.array_equal(lab[sure], np.argmin(D, axis=1)[sure])
+    assert abs(inertia - D.min(axis=1).sum()) <= 1e-3 * inertia
+    # overlapping clusters: local optima differ between seedings; compare quality, not labels
+    Y = rng.standard_normal((3000, 40)) + rng.standard_normal((15, 40))[rng.integers(0, 15, 3000)] * 1.5
+    best = min(mo.device_kmeans(Y, 15, seed=s)[2] for s in range(3))
+    ref = KMeans(n_clusters=15, random_state=0).fit(Y).inertia_
+    assert best <= 1.05 * ref, (best, ref)
+    out = mo.perform_clustering(Y, 15, 0, engine="device")
+    assert out.shape == (3000,) and out.min() >= 0 and out.max() < 15
