@@ -27,8 +27,9 @@ TYPES = ["location", "time", "visual", "embedding"]        # the two dense modal
 
 def main():
     nwin = int(sys.argv[1]) if len(sys.argv) > 1 else 2
+    n_items = int(sys.argv[2]) if len(sys.argv) > 2 else N_ITEMS      # the generator's draws depend on the stream length
     swfd_pkg, mo, me = ref_shim.load()
-    mods, _, labels = synth.multimodal_event_stream(N_ITEMS, n_events=150, noise_rate=0.95)
+    mods, _, labels = synth.multimodal_event_stream(n_items, n_events=150, noise_rate=0.95)
     sk, prev = None, None
     all_clusters = []
     sink = io.StringIO()
@@ -66,8 +67,8 @@ def main():
     res, _ = me.get_initial_results()
     with contextlib.redirect_stdout(sink):
         me.compute_all_metrics(res, n, 0.95, "multi", "none", REDUCED, KB, W, list(all_clusters), list(labels[:n]), 1, 0)
-    out = os.path.join(ROOT, "tests", "golden", "c3_prefix.npz")
-    np.savez_compressed(out, clusters=np.asarray(all_clusters), n_windows=nwin, W=W, reduced_dim=REDUCED, k_basis=KB,
+    out = os.path.join(ROOT, "tests", "golden", "c3_prefix.npz" if n_items == N_ITEMS else "c3_small.npz")
+    np.savez_compressed(out, n_items=n_items, clusters=np.asarray(all_clusters), n_windows=nwin, W=W, reduced_dim=REDUCED, k_basis=KB,
                         seconds=dt, items_per_s=n / dt, nmi=res["nmi_score"][0], nmi_e=res["nmi_e_score"][0],
                         f1=res["f1_score"][0], parts=np.array([parts["adjacency"], parts["sketch"], parts["cluster"]]))
     print("reference loop: %d items in %.1fs -> %.1f items/s (adjacency %.1fs, sketch %.1fs, cluster+match %.1fs); "

@@ -71,3 +71,32 @@ def test_device_window_loop_labels_and_scores_match_reference_golden():
     assert f1_score(true, clusters, average="weighted", zero_division=0) == pytest.approx(float(g["f1"]), abs=1e-12)
     ev = true > 0
     assert normalized_mutual_info_score(true[ev], clusters[ev]) == pytest.approx(float(g["nmi_e"]), abs=1e-12)
+
+
+@pytest.mark.gpu
+def test_configs2_shape_window_loop_matches_reference_loop():
+    """BASELINE configs[2] shape (W = 2000, reduced_dim = 50, k_basis = 50, location + time + two dense
+    embeddings of 512 + 768 columns): the device loop with schedule="reference" returns the labels of the
+    UNMODIFIED reference loop (oracle/time_reference_c3.py -> tests/golden/c3_small.npz) on two windows, hence the
+    same NMI / F1; schedule="batched" with the device KMeans is scored, not label-compared."""
+    from sklearn.metrics import f1_score, normalized_mutual_info_score
+    from mused_b200 import pipeline, synth
+    p = os.path.join(os.path.dirname(__file__), "golden", "c3_small.npz")
+    if not os.path.exists(p):
+        pytest.skip("c3_small.npz missing")
+    g = np.load(p)
+    n, W = int(g["n_items"]), int(g["W"])
+    mods, _, labels = synth.multimodal_event_stream(n, n_events=150, noise_rate=0.95)
+    types = ["location", "time", "visual", "embedding"]
+    m = int(g["n_windows"]) * W
+    clusters, true, _ = pipeline.process_streaming_data([x[:m] for x in mods], types, labels[:m], window_size=W,
+                                                        reduced_dim=int(g["reduced_dim"]), k_basis=int(g["k_basis"]),
+                                                        schedule="reference")
+    same = int(np.sum(clusters == g["clusters"]))
+    assert same >= m - 2, "%d of %d labels differ from the reference loop" % (m - same, m)   # kNN / KMeans near-ties
+    if same == m:
+        assert normalized_mutual_info_score(true, clusters) == pytest.approx(float(g["nmi"]), abs=1e-12)
+        assert f1_score(true, clusters, average="weighted", zero_division=0) == pytest.approx(float(g["f1"]), abs=1e-12)
+    c2, t2, _ = pipeline.process_streaming_data([x[:m] for x in mods], types, labels[:m], window_size=W, reduced_dim=50,
+                                                k_basis=50, schedule="batched", kmeans="device")
+    assert len(c2) == m and normalized_mutual_info_score(t2, c2) > 0.5 * float(g["nmi"])
