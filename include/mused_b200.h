@@ -258,6 +258,14 @@ int mused_topk_adjacency_f64(const double* feats, int64_t W, int64_t f, int64_t 
 int mused_contingency(const int32_t* prev, const int32_t* cur, int64_t n, int32_t P,
                       int32_t Q, int32_t* counts, void* stream);
 
+/* FD merge of an arbitrary stack of rows: thin SVD, top-l cut, shrink by the (l+1)-th squared singular value when
+ * the stack has more than l rows -- LMFD.__merge (swfd/lmfd.py:27-47), DI-FD's level merge (swfd/difd.py:117-127),
+ * FastFrequentDirectionsWithDump's full shrink (swfd/fastfdwithdump.py:98-108) and SlidingWindowFD.get
+ * (swfd/sliding_windows_frequent_directions.py:160-171).  rows: ng x d float64 DEVICE (ld); sketch l x d, sigma2 l,
+ * vt l x d (nullable): DEVICE.  Synchronises the stream. */
+int mused_fd_merge(const double* rows, int64_t ng, int64_t d, int64_t ld, int64_t ell, double* sketch, double* sigma2,
+                   double* vt, void* stream);
+
 /* KMeans of the reduced window, matrix_operations.py:149-153 (KMeans(n_clusters, random_state=seed).fit_predict)
  * entirely on the device: k-means++ seeding (D^2 sampling, counter-based RNG from `seed`), Lloyd iterations with
  * the assignment operator above and a deterministic centre update, until no label changes, the summed squared

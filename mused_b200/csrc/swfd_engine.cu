@@ -1167,6 +1167,60 @@ int mused_fd_get(mused_fd_t* h, double* sketch, double* sigma2, double* vt, doub
     return engine_get(*h->E, 0, false, sketch, sigma2, vt, delta, where, (cudaStream_t)stream);
 }
 
+// FD merge / shrink of an arbitrary stack of rows (the thin SVD + shrink + top-l cut that LMFD.__merge, lmfd.py:27-47,
+// DIFD, difd.py:117-127, FastFrequentDirectionsWithDump.fit, fastfdwithdump.py:98-108, and SlidingWindowFD.get,
+// sliding_windows_frequent_directions.py:160-171, all spell out with scipy.linalg.svd): rows (ng x d float64, device,
+// leading dimension ld) -> sketch (l x d: sqrt(s_i^2 - s_l^2) v_i^T, zero rows beyond the rank), sigma2 (l), vt (l x d,
+// nullable); s_l^2 is subtracted only when ng > l, as in the reference.  Scratch is allocated per call.
+int mused_fd_merge(const double* rows, int64_t ng, int64_t d, int64_t ld, int64_t ell, double* sketch, double* sigma2,
+                   double* vt, void* stream) {
+    MUSED_REQUIRE(rows && sketch && sigma2, "NULL argument");
+    MUSED_REQUIRE(ng >= 1 && d >= 1 && ld >= d && ell >= 1, "bad shape ng=%lld d=%lld l=%lld", (long long)ng, (long long)d, (long long)ell);
+    cudaStream_t st = (cudaStream_t)stream;
+    int dev = 0;
+    MUSED_CUDA(cudaGetDevice(&dev));
+    int sm = 148;
+    MUSED_CUDA(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev));
+    QueryScratch Q;
+    Q.ng_max = (int)std::max<int64_t>(ng, d) + 2;
+    Q.ng_max += Q.ng_max & 1;
+    Q.lda = Q.ng_max;
+    Q.rel_thr = 1e-11;
+    Q.plan_big();
+    std::vector<void*> allocs;
+    auto fail = [&](int code) { for (void* p : allocs) cudaFree(p); return code; };
+    auto alloc = [&](void** p, size_t bytes) -> int {
+        if (cudaMalloc(p, bytes) != cudaSuccess) { set_error("mused_fd_merge: cudaMalloc of %zu bytes failed", bytes); return MUSED_ERR_NOMEM; }
+        allocs.push_back(*p);
+        cudaMemsetAsync(*p, 0, bytes, st);
+        return 0;
+    };
+    int rc = 0;
+    double* out_s = nullptr; double* out_v = nullptr; double* out_2 = nullptr;
+    if ((rc = alloc((void**)&Q.M, sizeof(double) * (size_t)Q.ng_max * d)) || (rc = alloc((void**)&Q.G, sizeof(double) * (size_t)Q.lda * Q.lda)) ||
+        (rc = alloc((void**)&Q.Vq, sizeof(double) * (size_t)Q.lda * Q.lda)) || (rc = alloc((void**)&Q.cs, sizeof(double) * Q.ng_max)) ||
+        (rc = alloc((void**)&Q.eval, sizeof(double) * Q.npad_max)) || (rc = alloc((void**)&Q.perm, sizeof(int) * Q.npad_max)) ||
+        (rc = alloc((void**)&Q.lam, sizeof(double) * Q.npad_max)) || (rc = alloc((void**)&Q.VT, sizeof(double) * (size_t)Q.npad_max * Q.ldt)) ||
+        (rc = alloc((void**)&Q.mailL, sizeof(double) * Q.mail_count)) || (rc = alloc((void**)&Q.mailR, sizeof(double) * Q.mail_count)) ||
+        (rc = alloc((void**)&Q.sync, sizeof(unsigned long long) * QSYNC_WORDS)) || (rc = alloc((void**)&Q.counters, sizeof(int) * 64)) ||
+        (rc = alloc((void**)&Q.scr, sizeof(double) * 8)) || (rc = alloc((void**)&out_s, sizeof(double) * (size_t)ell * d)) ||
+        (rc = alloc((void**)&out_v, sizeof(double) * (size_t)ell * d)) || (rc = alloc((void**)&out_2, sizeof(double) * (size_t)ell)))
+        return fail(rc);
+    if (cudaMemcpy2DAsync(Q.M, (size_t)d * 8, rows, (size_t)ld * 8, (size_t)d * 8, (size_t)ng, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
+        set_error("mused_fd_merge: copying the stack failed");
+        return fail(MUSED_ERR_CUDA);
+    }
+    rc = merge_query(Q, (int)ng, d, (int)ell, sm, out_s, out_v, out_2, st);
+    if (rc) return fail(rc);
+    cudaMemcpyAsync(sketch, out_s, sizeof(double) * (size_t)ell * d, cudaMemcpyDeviceToDevice, st);
+    cudaMemcpyAsync(sigma2, out_2, sizeof(double) * (size_t)ell, cudaMemcpyDeviceToDevice, st);
+    if (vt) cudaMemcpyAsync(vt, out_v, sizeof(double) * (size_t)ell * d, cudaMemcpyDeviceToDevice, st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    for (void* p : allocs) cudaFree(p);
+    if (e != cudaSuccess) { set_error("mused_fd_merge failed: %s", cudaGetErrorString(e)); return MUSED_ERR_CUDA; }
+    return 0;
+}
+
 int mused_sym_eig(const double* G, int64_t n, int64_t ld, double* evals, double* vecs, int64_t ld_vecs,
                   int32_t* sweeps, void* stream) {
     MUSED_REQUIRE(G && evals && vecs, "NULL argument");
