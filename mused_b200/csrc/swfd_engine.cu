@@ -1169,7 +1169,7 @@ int mused_fd_get(mused_fd_t* h, double* sketch, double* sigma2, double* vt, doub
 
 // FD merge / shrink of an arbitrary stack of rows (the thin SVD + shrink + top-l cut that LMFD.__merge, lmfd.py:27-47,
 // DIFD, difd.py:117-127, FastFrequentDirectionsWithDump.fit, fastfdwithdump.py:98-108, and SlidingWindowFD.get,
-// sliding_windows_frequent_directions.py:160-171, all spell out with scipy.linalg.svd): rows (ng x d float64, device,
+// sliding_windows_frequent_directions.py:160-171, all spell out with a LAPACK thin SVD): rows (ng x d float64, device,
 // leading dimension ld) -> sketch (l x d: sqrt(s_i^2 - s_l^2) v_i^T, zero rows beyond the rank), sigma2 (l), vt (l x d,
 // nullable); s_l^2 is subtracted only when ng > l, as in the reference.  Scratch is allocated per call.
 int mused_fd_merge(const double* rows, int64_t ng, int64_t d, int64_t ld, int64_t ell, double* sketch, double* sigma2,
