@@ -243,6 +243,20 @@ int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float
 int mused_topk_adjacency(const float* feats, int64_t W, int64_t f, int64_t ld, int metric,
                          int64_t k, uint8_t* adj, void* stream);
 
+/* mused_topk_adjacency for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same
+ * arguments, same three kernels and the same result as mused_topk_adjacency; the W x W key matrix and the row
+ * norms live in a file-scope `static __device__` array of the library (4 MiB + 4 KiB, held by every GPU that loads
+ * the library until the process exits) instead of stream-ordered pool memory, and the call makes no cudaMalloc /
+ * cudaMallocAsync / cudaFree (the first call per device resolves the array's device address with
+ * cudaGetSymbolAddress).  Limit: W <= MUSED_TOPK_STATIC_MAX_W rows; a larger window is MUSED_ERR_ARG with a message
+ * naming the limit.  All calls on a device share the one array: calls that overlap on the GPU (different streams
+ * without an ordering between them) race -- serialise them.  Nothing in the array has to start at zero (both
+ * regions are rewritten for [0, W) before they are read). */
+#define MUSED_TOPK_STATIC_MAX_W 1024
+int mused_topk_adjacency_static(const float* feats, int64_t W, int64_t f, int64_t ld, int metric,
+                                int64_t k, uint8_t* adj, void* stream);
+
 /* Same operator for the two low-dimensional float64 modalities of
  * create_adjacency_matrix: metric HAVERSINE ("location", matrix_operations.py:22-30,
  * rows = (latitude, longitude) in degrees, k = k_basis + 1 there) and L1SUM

@@ -48,6 +48,7 @@ SYMBOLS = [
     "mused_topk_adjacency_f64", "mused_swfd_kernel_gaps", "mused_swfd_fit_timed",
     "mused_kmeans", "mused_fd_merge", "mused_comm_unique_id", "mused_swfd_attach_comm", "mused_swfd_comm_stats",
     "mused_swfd_fit_streams", "mused_swfd_get_stream", "mused_swfd_size_stream", "mused_swfd_debug_stream",
+    "mused_topk_adjacency_static",
 ]
 
 
@@ -102,6 +103,7 @@ def load():
     lib.mused_fd_get.argtypes = [vp, vp, vp, vp, C.POINTER(dbl), C.c_int, vp]
     lib.mused_assign.argtypes = [vp, i64, i64, i64, vp, i64, i64, C.c_int, C.c_float, vp, vp, vp]
     lib.mused_topk_adjacency.argtypes = [vp, i64, i64, i64, C.c_int, i64, vp, vp]
+    lib.mused_topk_adjacency_static.argtypes = [vp, i64, i64, i64, C.c_int, i64, vp, vp]
     lib.mused_fd_merge.argtypes = [vp, i64, i64, i64, i64, vp, vp, vp, vp]
     lib.mused_kmeans.argtypes = [vp, i64, i64, i64, i32, C.c_uint64, i32, dbl, vp, vp, C.POINTER(dbl), C.POINTER(i32), vp]
     lib.mused_contingency.argtypes = [vp, vp, i64, i32, i32, vp, vp]

@@ -2,9 +2,11 @@
 //   mused_assign          fused cosine|L2 + threshold + argmax|argmin (north_star operator;
 //                         nearest reference code matrix_operations.py:106, :286-289)
 //   mused_topk_adjacency  kNN -> 0/1 adjacency, OR-fused (matrix_operations.py:101-141)
+//   mused_topk_adjacency_static  the same with file-scope device scratch (no allocation; W <= 1024)
 //   mused_contingency     overlap counts of match_clusters (matrix_operations.py:169-172)
 #include <float.h>
 #include <stdlib.h>
+#include <atomic>
 #include "common.cuh"
 #include "assign_tc.cuh"
 
@@ -409,6 +411,29 @@ static int launch_assign_tc(const float* X, int64_t n, int64_t d, int64_t ld_x, 
     return 0;
 }
 
+// ---- scratch of mused_topk_adjacency_static: lives in the module image, one copy on every GPU that loads the
+// library, from load to exit.  [0, W*W) = the key matrix S (row stride W), [MAX_W^2, MAX_W^2 + W) = squared row norms.
+// The NAME below is a host-side stand-in in host code: the device address comes from cudaGetSymbolAddress.
+// MUSED_TOPK_STATIC_MAX_W (include/mused_b200.h) = 1024 rows -> 4 MiB + 4 KiB
+static __device__ __align__(256) float g_topk_static_scratch[(size_t)MUSED_TOPK_STATIC_MAX_W * MUSED_TOPK_STATIC_MAX_W +
+                                                             MUSED_TOPK_STATIC_MAX_W];
+
+// device address of the scratch on the CURRENT device, resolved once per device
+static int topk_static_scratch(float** out) {
+    static std::atomic<float*> addr[64];
+    int dev = 0;
+    MUSED_CUDA(cudaGetDevice(&dev));
+    MUSED_REQUIRE(dev >= 0 && dev < 64, "device ordinal %d out of range", dev);
+    float* p = addr[dev].load(std::memory_order_acquire);
+    if (!p) {
+        MUSED_CUDA(cudaGetSymbolAddress((void**)&p, g_topk_static_scratch));
+        MUSED_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a NULL scratch address");
+        addr[dev].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return 0;
+}
+
 extern "C" {
 
 int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float* C, int64_t k,
@@ -490,6 +515,39 @@ int mused_topk_adjacency(const float* feats, int64_t W, int64_t f, int64_t ld, i
     MUSED_CUDA(cudaGetLastError());
     MUSED_CUDA(cudaFreeAsync(S, st));
     MUSED_CUDA(cudaFreeAsync(n2, st));
+    mused_count_launches(3);
+    return 0;
+}
+
+// The same three launches as mused_topk_adjacency with the scratch in g_topk_static_scratch: no cudaMalloc /
+// cudaMallocAsync / cudaFree on this path.  Both scratch regions are fully overwritten for rows and columns
+// [0, W) before they are read, so nothing left by the previous call is ever consumed.
+int mused_topk_adjacency_static(const float* feats, int64_t W, int64_t f, int64_t ld, int metric, int64_t k,
+                                uint8_t* adj, void* stream) {
+    MUSED_REQUIRE(W >= 1 && f >= 1 && ld >= f && k >= 0, "bad shape");
+    MUSED_REQUIRE(feats && adj, "NULL argument");
+    MUSED_REQUIRE(metric == MUSED_METRIC_COSINE || metric == MUSED_METRIC_L2, "unknown metric %d", metric);
+    MUSED_REQUIRE(W <= MUSED_TOPK_STATIC_MAX_W,
+                  "window of %lld rows exceeds the static scratch of mused_topk_adjacency_static (max %d rows); "
+                  "use mused_topk_adjacency", (long long)W, MUSED_TOPK_STATIC_MAX_W);
+    if (k == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    float* scratch = nullptr;
+    if (int rc = topk_static_scratch(&scratch)) return rc;
+    float* S = scratch;
+    float* n2 = scratch + (size_t)MUSED_TOPK_STATIC_MAX_W * MUSED_TOPK_STATIC_MAX_W;
+    k_row_norm2_f32<<<(unsigned)((W + 7) / 8), 256, 0, st>>>(feats, W, f, ld, n2);
+    MUSED_CUDA(cudaGetLastError());
+    const long long tiles = ((W + AT - 1) / AT) * ((W + AT - 1) / AT);
+    const int sms = sm_count_of_current();
+    k_pair_keys<<<(int)std::min<long long>(tiles, 16ll * sms), 256, 0, st>>>(feats, W, f, ld, n2, metric, S);
+    MUSED_CUDA(cudaGetLastError());
+    // mused_topk_adjacency sets this attribute to ITS window's size on every call (possibly smaller than this one's,
+    // which would make the launch below invalid): set it here too.  An attribute of the function, not an allocation.
+    const size_t smem = (size_t)W * sizeof(float);
+    MUSED_CUDA(cudaFuncSetAttribute(k_topk_rows<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_topk_rows<float><<<(int)std::min<long long>(W, 8ll * sms), 256, smem, st>>>(S, W, k, adj);
+    MUSED_CUDA(cudaGetLastError());
     mused_count_launches(3);
     return 0;
 }
