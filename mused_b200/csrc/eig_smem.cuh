@@ -1,6 +1,5 @@
 // K3: batched symmetric eigensolve of the (2l x 2l) Gram matrices of the batched FD shrink.
-// One thread-block cluster per FD instance, the whole matrix in SHARED memory, one warp per
-// column pair.
+// One thread-block cluster per FD instance, the whole matrix in SHARED memory, 2 + 2 columns per warp step.
 //
 // The thin SVD of [sketch; batch] that the reference takes with LAPACK
 // (swfd/frequent_directions.py:55) is replaced by the eigen-decomposition of G = R R^T.  One-sided
@@ -8,18 +7,17 @@
 // columns, W V -> V Lambda, so column norms converge to the eigenvalues and w_j / lambda_j to the
 // eigenvectors; no separate V is carried.
 //
-// Layout: CTA c of the cluster (n2 / 32 CTAs, 512 threads) holds 32 columns, two blocks of 16, all
-// n2 rows, column-major in shared memory.  A STEP rotates 16 disjoint column pairs, one per warp:
-// the lanes of the warp split the rows (n2 / 32 each, 128-bit shared-memory accesses), one packed
-// dot product + one 5-stage shuffle reduction + the angle + the rotation, then __syncthreads.
-// Squared column norms are cached and updated by the rotation (only the cross product is reduced).
-// A ROUND = the 16 steps that pair every column of the CTA's first block with every column of its
-// second block; between rounds the blocks move through distributed shared memory following the
-// round-robin tournament on 2 NC blocks (block 0 fixed, 2 NC - 1 rounds: every block pair meets
-// once); pairs inside a block are rotated once per sweep (15 steps).  A sweep is therefore
-// n2 - 1 steps (255 at l = 128) of ~one rotation latency each.  Round 1 of this repo kept the
-// matrix in the REGISTERS of 4 warps per CTA (8 columns per warp, four rotations interleaved per
-// warp): 1 300 cycles per step, one warp per scheduler; here 16 warps per SM issue side by side.
+// Layout: CTA c of the cluster (n2 / 32 CTAs, 256 threads = 8 warps, two CTAs per SM up to n2 = 256) holds 32
+// columns, two blocks of 16, all n2 rows, column-major in shared memory.  In a ROUND warp w keeps columns 2w, 2w+1
+// of the CTA's first block in registers and the column pairs of the second block pass by through shared memory:
+// 8 STEPS per round, each a 2 x 2 block of rotations (four inner products, packed FFMA2 on float32, one 5-stage
+// shuffle reduction, the angles, the rotations, 128-bit shared-memory accesses), then __syncthreads.  Squared column
+// norms are cached and follow the rotations (only the cross products are reduced).  Between rounds the blocks move
+// through distributed shared memory following the round-robin tournament on 2 NC blocks (block 0 fixed, 2 NC - 1
+// rounds: every block pair meets once); pairs inside a block are rotated at the head of the sweep (7 steps on 8
+// column pairs per block + the pair inside each 2-column unit).  A sweep at l = 128 is 15 rounds x 8 steps + the
+// head, ~214 k cycles in float32.  Round 1 of this repo kept the matrix in the REGISTERS of 4 warps per CTA
+// (8 columns per warp): one warp per scheduler; DESIGN.md 4b lists what else was measured.
 //
 // Mixed precision as before: float32 sweeps on G / max|G| until the largest cosine of a sweep is
 // <= tol32, V32 = normalised columns, W = G V32 in float64 (G re-read from L2), float64 sweeps
