@@ -229,10 +229,15 @@ int mused_fd_get(mused_fd_t* h, double* sketch, double* sigma2, double* vt, doub
  * metric COSINE: label = argmax_j cos(x, c_j) if that cosine >= tau else -1;
  * metric L2:     label = argmin_j ||x - c_j||  if that distance <= tau else -1
  *                (tau < 0 disables the threshold).  Ties -> lowest j.
- * score (nullable): best cosine / best distance. */
+ * score (nullable): best cosine / best distance.
+ * With score == NULL and metric COSINE the call takes the bandwidth path: one TF32 screening pass on the tensor
+ * cores, then float32 re-scoring of exactly the rows whose decision (winner or threshold) lies inside the
+ * screening error bound (|error of a cosine| <= 1.1e-3); the labels are those of the float32-exact path. */
 int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float* C,
                  int64_t k, int64_t ld_c, int metric, float tau, int32_t* labels,
                  float* score, void* stream);
+/* Diagnostics of the call above: rows re-scored after screening, cumulative on the current device (synchronises). */
+int mused_assign_pending(uint64_t* n_rows);
 
 /* kNN adjacency of one dense modality, OR-accumulated into a fused uint8
  * W x W matrix (create_adjacency_matrix numeric branches

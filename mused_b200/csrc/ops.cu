@@ -392,10 +392,11 @@ static int sm_count_of_current() {
 using namespace mused;
 extern "C" void mused_count_launches(uint64_t n);
 
-// tensor-core path of mused_assign (assign_tc.cuh); *done = false -> shape not eligible
-template <int MH, int NST>
+// tensor-core path of mused_assign (assign_tc.cuh)
+template <int MH, int NST, int PASSES = 3>
 static int launch_assign_tc(const float* X, int64_t n, int64_t d, int64_t ld_x, int NP, const float* Chi,
-                            const float* Clo, atc::Args& A, cudaStream_t st) {
+                            const float* Clo, atc::Args& A, cudaStream_t st, int max_ctas = 0) {
+    using CF = atc::Cfg<MH, NST, PASSES>;
     CUtensorMap tx, thi, tlo;
     if (encode_tmap_f32_2d(&tx, X, (uint64_t)n, (uint64_t)d, (uint64_t)ld_x, 128) != CUDA_SUCCESS ||
         encode_tmap_f32_2d(&thi, Chi, (uint64_t)NP, (uint64_t)d, (uint64_t)d, (uint32_t)NP) != CUDA_SUCCESS ||
@@ -403,11 +404,28 @@ static int launch_assign_tc(const float* X, int64_t n, int64_t d, int64_t ld_x, 
         set_error("cuTensorMapEncodeTiled failed for the assignment operands");
         return MUSED_ERR_CUDA;
     }
-    const size_t smem = atc::Cfg<MH, NST>::smem_bytes(NP);
-    MUSED_CUDA(cudaFuncSetAttribute(atc::k_assign_tc<MH, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem = CF::smem_bytes(NP);
+    MUSED_CUDA(cudaFuncSetAttribute(atc::k_assign_tc<MH, NST, PASSES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long tiles = (n + MH * 128 - 1) / (MH * 128);
-    atc::k_assign_tc<MH, NST><<<(unsigned)tiles, atc::Cfg<MH, NST>::NTHREADS, smem, st>>>(tx, thi, tlo, A);
+    const long long grid = max_ctas > 0 ? std::min<long long>(tiles, max_ctas) : tiles;   // max_ctas: persistent tile loop
+    atc::k_assign_tc<MH, NST, PASSES><<<(unsigned)grid, CF::NTHREADS, smem, st>>>(tx, thi, tlo, A);
     MUSED_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// rows the screening kernel left to k_assign_rescore, cumulative per device (mused_assign_pending)
+static __device__ unsigned long long g_assign_pending;
+static int assign_pending_addr(unsigned long long** out) {
+    static std::atomic<unsigned long long*> addr[64];
+    int dev = 0;
+    MUSED_CUDA(cudaGetDevice(&dev));
+    MUSED_REQUIRE(dev >= 0 && dev < 64, "device ordinal %d out of range", dev);
+    unsigned long long* p = addr[dev].load(std::memory_order_acquire);
+    if (!p) {
+        MUSED_CUDA(cudaGetSymbolAddress((void**)&p, g_assign_pending));
+        addr[dev].store(p, std::memory_order_release);
+    }
+    *out = p;
     return 0;
 }
 
@@ -458,15 +476,43 @@ int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float
         A.n = n; A.k = (int)k; A.NP = NP; A.kblocks = (int)(d / 32); A.metric = metric; A.tau = tau;
         A.cn2 = c2; A.labels = labels; A.score = score;
         const int sms = sm_count_of_current();
+        const size_t cap = 227u * 1024u;
+        int rc;
+        // labels-only cosine call: one-pass TF32 screening (persistent, one CTA per SM) + float32 re-scoring of the rows
+        // whose decision is inside the screening error bound (assign_tc.cuh); MUSED_ASSIGN_EXACT=1 forces 3xTF32
+        static int exact = -1;
+        if (exact < 0) exact = getenv("MUSED_ASSIGN_EXACT") ? atoi(getenv("MUSED_ASSIGN_EXACT")) : 0;
+        if (metric == MUSED_METRIC_COSINE && score == nullptr && !exact && ld_c % 4 == 0 && ((uintptr_t)C & 15) == 0) {
+            // 256-row tiles once every SM has one (centroid slices shared by two accumulators), else 128-row tiles;
+            // grid = one persistent CTA per SM
+            const bool big = (n + 255) / 256 >= sms;
+            if (big && atc::Cfg<2, 4, 1>::smem_bytes(NP) <= cap) rc = launch_assign_tc<2, 4, 1>(X, n, d, ld_x, NP, Chi, Chi, A, st, sms);
+            else if (big && atc::Cfg<2, 3, 1>::smem_bytes(NP) <= cap) rc = launch_assign_tc<2, 3, 1>(X, n, d, ld_x, NP, Chi, Chi, A, st, sms);
+            else if (atc::Cfg<1, 4, 1>::smem_bytes(NP) <= cap) rc = launch_assign_tc<1, 4, 1>(X, n, d, ld_x, NP, Chi, Chi, A, st, sms);
+            else rc = launch_assign_tc<1, 3, 1>(X, n, d, ld_x, NP, Chi, Chi, A, st, sms);
+            if (!rc) {
+                unsigned long long* pend = nullptr;
+                rc = assign_pending_addr(&pend);
+                if (!rc) {
+                    const int grid = (int)std::min<long long>((n + 255) / 256, 8ll * sms);
+                    atc::k_assign_rescore<<<grid, 256, 0, st>>>(X, n, d, ld_x, C, (int)k, ld_c, c2, tau, labels, pend);
+                    if (cudaGetLastError() != cudaSuccess) { set_error("k_assign_rescore launch failed"); rc = MUSED_ERR_CUDA; }
+                }
+            }
+            MUSED_CUDA(cudaFreeAsync(Chi, st));
+            MUSED_CUDA(cudaFreeAsync(Clo, st));
+            MUSED_CUDA(cudaFreeAsync(c2, st));
+            if (rc) return rc;
+            mused_count_launches(3);
+            return 0;
+        }
         // tile shape (measured on B200, k = 150, d = 1024): two 128-row accumulators per CTA halve the
         // centroid re-reads from L2 and win once every SM has a tile (2.43 TB/s at 1M rows against
         // 2.08 TB/s); a window-sized call (10k rows) wants more, smaller CTAs with a deeper pipeline.
         static int shape = -1;
         if (shape < 0) shape = getenv("MUSED_ASSIGN_SHAPE") ? atoi(getenv("MUSED_ASSIGN_SHAPE")) : 0;
-        const size_t cap = 227u * 1024u;
         const bool fits22 = atc::Cfg<2, 2>::smem_bytes(NP) <= cap;
         const bool big = (n + 255) / 256 >= sms;
-        int rc;
         if (fits22 && (shape == 22 || (shape == 0 && big))) rc = launch_assign_tc<2, 2>(X, n, d, ld_x, NP, Chi, Clo, A, st);
         else if (shape != 12 && atc::Cfg<1, 4>::smem_bytes(NP) <= cap) rc = launch_assign_tc<1, 4>(X, n, d, ld_x, NP, Chi, Clo, A, st);
         else if (shape != 12 && atc::Cfg<1, 3>::smem_bytes(NP) <= cap) rc = launch_assign_tc<1, 3>(X, n, d, ld_x, NP, Chi, Clo, A, st);
@@ -488,6 +534,14 @@ int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float
     MUSED_CUDA(cudaGetLastError());
     MUSED_CUDA(cudaFreeAsync(cn2, st));
     mused_count_launches(2);
+    return 0;
+}
+
+int mused_assign_pending(uint64_t* n_rows) {
+    MUSED_REQUIRE(n_rows, "NULL argument");
+    unsigned long long v = 0;
+    MUSED_CUDA(cudaMemcpyFromSymbol(&v, g_assign_pending, sizeof(v)));
+    *n_rows = (uint64_t)v;
     return 0;
 }
 

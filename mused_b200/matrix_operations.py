@@ -41,13 +41,14 @@ def cosine_assign(X, centroids, threshold, *, metric="cosine", device="cuda:0", 
         raise ValueError("X (n x d) and centroids (k x d) must share d")
     n, d = Xd.shape
     labels = torch.empty(n, dtype=torch.int32, device=Xd.device)
-    score = torch.empty(n, dtype=torch.float32, device=Xd.device)
+    # labels only -> NULL score: the library takes its screening + re-scoring path (bandwidth-bound, same labels)
+    score = torch.empty(n, dtype=torch.float32, device=Xd.device) if return_score else None
     with torch.cuda.device(Xd.device):
         st = torch.cuda.current_stream().cuda_stream
         _lib.check(lib.mused_assign(Xd.data_ptr(), n, d, Xd.stride(0) if n > 1 else d, Cd.data_ptr(),
                                     Cd.shape[0], Cd.stride(0) if Cd.shape[0] > 1 else d,
                                     _METRIC[metric], float(threshold), labels.data_ptr(),
-                                    score.data_ptr(), st))
+                                    score.data_ptr() if return_score else None, st))
     return (labels, score) if return_score else labels
 
 

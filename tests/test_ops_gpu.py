@@ -66,6 +66,48 @@ def test_cosine_assign_edge_cases():
     assert lab.cpu().tolist() == [-1, 0, -1, 0]
 
 
+@pytest.mark.parametrize("kind,n,d,k,tau", [("clustered", 40000, 512, 150, 0.5), ("noise", 30000, 1024, 150, 0.08),
+                                            ("noise", 5000, 256, 3, -1.0), ("dups", 3000, 128, 40, 0.2)])
+def test_cosine_assign_screening_path_gives_the_exact_labels(kind, n, d, k, tau):
+    """Labels-only cosine calls take one TF32 screening pass + float32 re-scoring of the undecided rows
+    (assign_tc.cuh).  Its labels must be the float64 oracle's outside the near-tie margin -- on clustered data
+    (almost nothing re-scored), on pure noise with the threshold in the bulk of the best cosines (a large share
+    re-scored, every pending type) and with duplicated centroids (exact ties -> lowest index)."""
+    import ctypes as C_
+    from mused_b200 import matrix_operations as mo, _lib
+    rng = np.random.default_rng(k + d)
+    C = rng.standard_normal((k, d)).astype(np.float32)
+    if kind == "clustered":
+        X = (C[rng.integers(0, k, n)] + 0.8 * rng.standard_normal((n, d))).astype(np.float32)
+        X[::3] = rng.standard_normal((len(X[::3]), d))
+    elif kind == "noise":
+        X = rng.standard_normal((n, d)).astype(np.float32)
+        X[7] = 0.0
+    else:
+        C[k // 2:] = C[:k - k // 2]                      # every centroid twice
+        X = (C[rng.integers(0, k, n)] + 0.5 * rng.standard_normal((n, d))).astype(np.float32)
+    ref, best, gap = ops_oracle.cosine_assign(X, C, tau)
+    lib = _lib.load()
+    p0, p1 = C_.c_uint64(0), C_.c_uint64(0)
+    _lib.check(lib.mused_assign_pending(C_.byref(p0)))
+    lab = mo.cosine_assign(X, C, tau).cpu().numpy()                       # screening + re-score
+    _lib.check(lib.mused_assign_pending(C_.byref(p1)))
+    lab3, _ = mo.cosine_assign(X, C, tau, return_score=True)              # 3xTF32
+    lab3 = lab3.cpu().numpy()
+    assert lab.min() >= -1 and lab.max() < k                              # no pending code survives
+    sure = (gap > TIE) & (np.abs(best - tau) > TIE)
+    if kind == "dups":
+        assert np.array_equal(lab, lab3)                                  # exact ties resolved to the lowest index by both
+        assert np.all(lab[lab >= 0] < k - k // 2)
+    else:
+        assert np.array_equal(lab[sure], ref[sure])
+        assert np.array_equal(lab[sure], lab3[sure])
+    frac = (p1.value - p0.value) / n
+    print("%s: %.2f %% of the rows re-scored" % (kind, 100 * frac))
+    if kind == "clustered":
+        assert frac < 0.02
+
+
 @pytest.mark.parametrize("n,d,k", [(500, 50, 12), (64, 7, 3)])
 def test_l2_assign(n, d, k):
     from mused_b200 import matrix_operations as mo

@@ -1,5 +1,6 @@
 """Summarise `ncu --set full` reports into tracked files under profiles/ (run in the build container):
    python tools/ncu_summarise.py gpurun_out/r02_chunk.ncu-rep gpurun_out/r02_chunk_c3.ncu-rep ...
+   python tools/ncu_summarise.py --append gpurun_out/r02_strict.ncu-rep      (adds to the committed files)
 writes profiles/r02_ncu_full_summary.csv (one row per profiled launch: duration, DRAM bytes, tensor pipe,
 issue activity, registers, grid) and profiles/r02_ncu_dominant.json (per kernel name, from the FIRST report:
 what bench.py's `roofline.traffic` / `roofline.ncu` are read from) plus the stall table of k_eig_jacobi."""
@@ -37,7 +38,17 @@ def raw(path):
 
 def main():
     summary, dominant = [], {}
-    for ri, path in enumerate(sys.argv[1:]):
+    args = sys.argv[1:]
+    append = "--append" in args          # keep what profiles/ already holds (earlier captures), add these reports
+    args = [a for a in args if a != "--append"]
+    csv_path = os.path.join(ROOT, "profiles", "r02_ncu_full_summary.csv")
+    old_rows = []
+    if append:
+        with open(csv_path) as f:
+            old_rows = [l.rstrip("\n") for l in f if not l.startswith("#")][1:]
+        with open(os.path.join(ROOT, "profiles", "r02_ncu_dominant.json")) as f:
+            dominant = json.load(f)
+    for ri, path in enumerate(args):
         hdr, units, rows = raw(path)
         ix = {h: i for i, h in enumerate(hdr)}
         stall = [h for h in hdr if h.startswith("smsp__average_warps_issue_stalled_") and h.endswith("_per_issue_active.ratio")]
@@ -53,7 +64,7 @@ def main():
                         rec[key] = None
             summary.append(rec)
             base = re.sub(r"<.*", "", name)
-            if ri == 0 and base not in dominant:
+            if (ri == 0 or append) and base not in dominant:
                 d = {"dram_bytes_per_launch": (rec.get("dram_read") or 0) + (rec.get("dram_write") or 0),
                      "duration_ms_under_ncu": 1e3 * rec["duration"], "issue_active_pct": rec.get("issue_active_pct"),
                      "tensor_pipe_pct": rec.get("tensor_pipe_pct"), "warp_instructions": rec.get("warp_instructions"),
@@ -69,6 +80,8 @@ def main():
     with open(os.path.join(ROOT, "profiles", "r02_ncu_full_summary.csv"), "w") as f:
         f.write("# ncu --set full --clock-control none --cache-control none (tools/ncu_capture.sh); seconds / bytes / percent\n")
         f.write(",".join(keys) + "\n")
+        for l in old_rows:
+            f.write(l + "\n")
         for rec in summary:
             f.write(",".join("" if rec.get(k) is None else (("%.6g" % rec[k]) if isinstance(rec[k], float) else str(rec[k]))
                              for k in keys) + "\n")
