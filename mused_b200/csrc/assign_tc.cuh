@@ -43,6 +43,8 @@ struct Args {
     const float* cn2;                  // [NP] squared centroid norms (0 for padding)
     int* labels;
     float* score;                      // nullable
+    uint32_t* cmask;                   // screening: [n][nw] bit masks of the keys within 2 eps of the row's best
+    int nw;                            //            (read back by k_assign_rescore for rows with > 3 candidates)
 };
 
 constexpr float SCREEN_EPS = 1.1e-3f;  // >= 2^-10 (two RNA-rounded TF32 operands) + fp32 accumulation over d <= 64k
@@ -263,6 +265,18 @@ k_assign_tc(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CU
                         }
                     }
                 }
+                if (__any_sync(0xffffffffu, cnt > 3)) {                          // rare: leave those rows' masks for the re-score
+                    for (int c0 = 0; c0 < NP; c0 += 32) {
+                        uint32_t v[32];
+                        umma::tmem_ld32(trow + c0, v);
+                        umma::tmem_ld_wait();
+                        uint32_t m = 0;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (c0 + j < A.k && __uint_as_float(v[j]) * cscale[c0 + j] >= thr) m |= 1u << j;
+                        if (cnt > 3 && r < A.n) A.cmask[(size_t)r * A.nw + (c0 >> 5)] = m;
+                    }
+                }
                 umma::tc_fence_before();
                 umma::mbar_arrive(accfree);
                 if (r < A.n) {
@@ -318,7 +332,7 @@ k_assign_tc(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CU
 
 // Second step of the screening path: every label slot holding a pending code is decided in float32 FMA arithmetic
 // from the row itself (PEND_ONE: the threshold of a known winner; PEND_PAIR / PEND_TRIPLE: the candidates named in
-// the code; PEND_FULL: all k).  A warp scans 32 label slots, then takes its pending rows one at a time, lanes
+// the code; PEND_FULL: the candidates of the row's bit mask).  A warp scans 32 label slots, then takes its pending rows one at a time, lanes
 // striding the d columns; up to four centroids per pass over the row so their loads are in flight together.
 __device__ __forceinline__ void rescore_dots(const float* __restrict__ x, const float* __restrict__ C, long long ldc,
                                              const int (&j)[4], int nj, long long d, int lane, float (&dot)[4], float& xn2) {
@@ -348,6 +362,7 @@ __device__ __forceinline__ void rescore_dots(const float* __restrict__ x, const 
 __global__ void __launch_bounds__(256) k_assign_rescore(const float* __restrict__ X, long long n, long long d, long long ldx,
                                                         const float* __restrict__ C, int k, long long ldc,
                                                         const float* __restrict__ cn2, float tau, int* __restrict__ labels,
+                                                        const uint32_t* __restrict__ cmask, int nw,
                                                         unsigned long long* __restrict__ n_pending) {
     const int lane = threadIdx.x & 31;
     const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
@@ -378,10 +393,19 @@ __global__ void __launch_bounds__(256) k_assign_rescore(const float* __restrict_
                     }
                 }
             } else {
-                for (int j0 = 0; j0 < k; j0 += 4) {
-                    const int nj = k - j0 < 4 ? k - j0 : 4;
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) j[c] = j0 + (c < nj ? c : 0);
+                // more than three candidates: walk the row's candidate mask, four at a time, ascending index
+                int w = 0;
+                uint32_t m = cmask[(size_t)r * nw];
+                for (;;) {
+                    int nj = 0;
+                    while (nj < 4) {
+                        while (!m && w + 1 < nw) m = cmask[(size_t)r * nw + ++w];
+                        if (!m) break;
+                        j[nj++] = 32 * w + __ffs(m) - 1;
+                        m &= m - 1;
+                    }
+                    if (nj == 0) break;
+                    for (int c = nj; c < 4; ++c) j[c] = j[0];
                     rescore_dots(x, C, ldc, j, nj, d, lane, dot, xn2);
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
@@ -391,6 +415,7 @@ __global__ void __launch_bounds__(256) k_assign_rescore(const float* __restrict_
                             if (key > best) { best = key; bidx = j[c]; }                               // ascending index
                         }
                     }
+                    if (nj < 4) break;
                 }
             }
             const float sc = best * rsqrtf(xn2 > 0.f ? xn2 : 1.f);

@@ -474,7 +474,7 @@ int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float
         MUSED_CUDA(cudaGetLastError());
         atc::Args A;
         A.n = n; A.k = (int)k; A.NP = NP; A.kblocks = (int)(d / 32); A.metric = metric; A.tau = tau;
-        A.cn2 = c2; A.labels = labels; A.score = score;
+        A.cn2 = c2; A.labels = labels; A.score = score; A.cmask = nullptr; A.nw = 0;
         const int sms = sm_count_of_current();
         const size_t cap = 227u * 1024u;
         int rc;
@@ -486,6 +486,8 @@ int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float
             // 256-row tiles once every SM has one (centroid slices shared by two accumulators), else 128-row tiles;
             // grid = one persistent CTA per SM
             const bool big = (n + 255) / 256 >= sms;
+            A.nw = NP / 32 + (NP % 32 != 0);
+            MUSED_CUDA(cudaMallocAsync((void**)&A.cmask, sizeof(uint32_t) * (size_t)n * A.nw, st));
             if (big && atc::Cfg<2, 4, 1>::smem_bytes(NP) <= cap) rc = launch_assign_tc<2, 4, 1>(X, n, d, ld_x, NP, Chi, Chi, A, st, sms);
             else if (big && atc::Cfg<2, 3, 1>::smem_bytes(NP) <= cap) rc = launch_assign_tc<2, 3, 1>(X, n, d, ld_x, NP, Chi, Chi, A, st, sms);
             else if (atc::Cfg<1, 4, 1>::smem_bytes(NP) <= cap) rc = launch_assign_tc<1, 4, 1>(X, n, d, ld_x, NP, Chi, Chi, A, st, sms);
@@ -495,10 +497,11 @@ int mused_assign(const float* X, int64_t n, int64_t d, int64_t ld_x, const float
                 rc = assign_pending_addr(&pend);
                 if (!rc) {
                     const int grid = (int)std::min<long long>((n + 255) / 256, 8ll * sms);
-                    atc::k_assign_rescore<<<grid, 256, 0, st>>>(X, n, d, ld_x, C, (int)k, ld_c, c2, tau, labels, pend);
+                    atc::k_assign_rescore<<<grid, 256, 0, st>>>(X, n, d, ld_x, C, (int)k, ld_c, c2, tau, labels, A.cmask, A.nw, pend);
                     if (cudaGetLastError() != cudaSuccess) { set_error("k_assign_rescore launch failed"); rc = MUSED_ERR_CUDA; }
                 }
             }
+            MUSED_CUDA(cudaFreeAsync(A.cmask, st));
             MUSED_CUDA(cudaFreeAsync(Chi, st));
             MUSED_CUDA(cudaFreeAsync(Clo, st));
             MUSED_CUDA(cudaFreeAsync(c2, st));

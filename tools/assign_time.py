@@ -11,6 +11,13 @@ from mused_b200 import matrix_operations as mo, _lib
 d, k = 1024, 150
 peak = json.load(open("MEASURED_PEAKS.json"))["hbm_gbs"]
 lib = _lib.load()
+try:
+    import pynvml
+    pynvml.nvmlInit()
+    _h = pynvml.nvmlDeviceGetHandleByIndex(0)
+    sm_mhz = lambda: pynvml.nvmlDeviceGetClockInfo(_h, pynvml.NVML_CLOCK_SM)
+except Exception:
+    sm_mhz = lambda: -1
 
 
 def pending():
@@ -36,11 +43,13 @@ for n in [int(a) for a in sys.argv[1:]] or [10000, 1 << 20]:
             torch.cuda.synchronize()
             p0 = pending()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            reps = 5
+            reps = 20
             e0.record()
             for _ in range(reps):
                 out = mo.cosine_assign(X, C, tau, return_score=score)
-            e1.record(); torch.cuda.synchronize()
+            e1.record()
+            mhz = sm_mhz()                       # sampled while the last launches are still running
+            torch.cuda.synchronize()
             lab = out[0] if score else out
             ms = e0.elapsed_time(e1) / reps
             frac = (pending() - p0) / reps / n
@@ -52,6 +61,6 @@ for n in [int(a) for a in sys.argv[1:]] or [10000, 1 << 20]:
             ref = torch.where(top2[:, 0] >= tau, S.argmax(1), torch.full((m,), -1, device="cuda"))
             sure = ((top2[:, 0] - top2[:, 1]) > 2e-5) & ((top2[:, 0] - tau).abs() > 2e-5)
             bad = int((lab[:m].long()[sure] != ref[sure]).sum())
-            print("n=%d %-6s %-22s %.3f ms  %.1f GB/s (%.1f%% of measured HBM peak)  re-scored %.2f%%  mismatches(sure rows)=%d/%d" %
+            print("n=%d %-6s %-22s %.3f ms  %.1f GB/s (%.1f%% of measured HBM peak)  re-scored %.2f%%  mismatches(sure rows)=%d/%d  SM %d MHz" %
                   (n, kind, "3xTF32 (with score)" if score else "screen + re-score", ms, gb / ms * 1e3,
-                   100 * gb / ms * 1e3 / peak, 100 * frac, bad, int(sure.sum())), flush=True)
+                   100 * gb / ms * 1e3 / peak, 100 * frac, bad, int(sure.sum()), mhz), flush=True)
