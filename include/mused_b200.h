@@ -295,6 +295,17 @@ int mused_fd_merge(const double* rows, int64_t ng, int64_t d, int64_t ld, int64_
 int mused_kmeans(const float* X, int64_t n, int64_t d, int64_t ld, int32_t k, uint64_t seed, int32_t max_iter, double tol,
                  float* centroids, int32_t* labels, double* inertia, int32_t* n_iter, void* stream);
 
+/* perform_svd_reduction (matrix_operations.py:143-147: TruncatedSVD(n_components, random_state=seed).fit_transform),
+ * the reducer of the reference's sSVDMC approaches (main.py:79, :146), as sklearn's randomized SVD on the device:
+ * n_iter power iterations from the Gaussian test matrix omega (n x q float64 DEVICE, row-major, q = n_components +
+ * n_oversamples; the caller draws it with numpy's RandomState(seed).normal so that it is sklearn's), re-conditioned
+ * by Cholesky-QR, B = Q^T M, V^T = right singular vectors of B with svd_flip's sign rule, Xt = M V (m x k, ld_xt).
+ * M: m x n (ld), dtype MUSED_U8 (the fused 0/1 adjacency) or MUSED_F64, DEVICE, m >= n.  sigma (k, nullable) and
+ * vt (k x n, ld_vt, nullable): DEVICE.  1 <= k <= q <= min(n, 160).  Synchronises the stream. */
+int mused_svd_reduce(const void* M, int dtype, int64_t m, int64_t n, int64_t ld, const double* omega, int32_t q,
+                     int32_t k, int32_t n_iter, double* Xt, int64_t ld_xt, double* sigma, double* vt, int64_t ld_vt,
+                     void* stream);
+
 /* Symmetric eigen-decomposition of a positive semi-definite Gram matrix
  * (what replaces scipy.linalg.svd(..., lapack_driver="gesvd") of the stacked
  * rows in SlidingWindowFD.get, sliding_windows_frequent_directions.py:160, and

@@ -48,7 +48,7 @@ SYMBOLS = [
     "mused_topk_adjacency_f64", "mused_swfd_kernel_gaps", "mused_swfd_fit_timed",
     "mused_kmeans", "mused_fd_merge", "mused_comm_unique_id", "mused_swfd_attach_comm", "mused_swfd_comm_stats",
     "mused_swfd_fit_streams", "mused_swfd_get_stream", "mused_swfd_size_stream", "mused_swfd_debug_stream",
-    "mused_topk_adjacency_static", "mused_assign_pending",
+    "mused_topk_adjacency_static", "mused_assign_pending", "mused_svd_reduce",
 ]
 
 
@@ -102,6 +102,7 @@ def load():
     lib.mused_fd_flush.argtypes = [vp, vp]
     lib.mused_fd_get.argtypes = [vp, vp, vp, vp, C.POINTER(dbl), C.c_int, vp]
     lib.mused_assign.argtypes = [vp, i64, i64, i64, vp, i64, i64, C.c_int, C.c_float, vp, vp, vp]
+    lib.mused_svd_reduce.argtypes = [vp, C.c_int, i64, i64, i64, vp, i32, i32, i32, vp, i64, vp, vp, i64, vp]
     lib.mused_assign_pending.argtypes = [C.POINTER(C.c_uint64)]
     lib.mused_topk_adjacency.argtypes = [vp, i64, i64, i64, C.c_int, i64, vp, vp]
     lib.mused_topk_adjacency_static.argtypes = [vp, i64, i64, i64, C.c_int, i64, vp, vp]

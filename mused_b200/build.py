@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libmused_b200.so")
 STAMP = os.path.join(HERE, ".libmused_b200.stamp")
-SOURCES = ["swfd_engine.cu", "bswfd.cu", "ops.cu"]
+SOURCES = ["swfd_engine.cu", "bswfd.cu", "ops.cu", "svd_reduce.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--expt-extended-lambda", "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC",

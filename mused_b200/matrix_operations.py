@@ -152,6 +152,43 @@ def fuse_matrices(matrices, *, device="cuda:0"):
     return out.cpu().numpy().astype(int)
 
 
+def perform_svd_reduction(matrix, reduced_dim, seed, *, n_iter=5, n_oversamples=10, device="cuda:0",
+                          return_model=False):
+    """matrix_operations.py:143-147: ``TruncatedSVD(n_components=min(reduced_dim, n_features - 1),
+    random_state=seed).fit_transform(matrix)`` as a randomized SVD on the device (C ABI ``mused_svd_reduce``).
+
+    ``matrix``: the fused adjacency, a CUDA uint8 tensor (``fused_adjacency``) or anything array-like (taken as
+    float64).  The Gaussian test matrix is drawn here with numpy's ``RandomState(seed).normal`` exactly as sklearn's
+    ``randomized_range_finder`` draws it, so the same seed starts from the same subspace; sklearn re-conditions the
+    basis by LU, the device by Cholesky-QR -- the same range, results equal up to rounding
+    (tests/test_svd_reduce_gpu.py).  Returns the W x k reduced matrix (numpy float64) [and singular values, V^T]."""
+    lib = _lib.load()
+    if isinstance(matrix, torch.Tensor) and matrix.dtype == torch.uint8:
+        M, dt = matrix.to(device).contiguous(), _lib.U8
+    else:
+        src = matrix.detach().cpu().numpy() if isinstance(matrix, torch.Tensor) else np.asarray(matrix)
+        M, dt = torch.as_tensor(np.ascontiguousarray(src, dtype=np.float64)).to(device), _lib.F64
+    m, n = M.shape
+    if m < n:
+        raise ValueError("perform_svd_reduction on the device takes matrices with rows >= columns (got %d x %d)" % (m, n))
+    k = min(int(reduced_dim), n - 1)
+    q = min(k + int(n_oversamples), n)
+    if q > 160:
+        raise ValueError("n_components + n_oversamples = %d exceeds the device limit of 160" % q)
+    omega = np.random.RandomState(seed).normal(size=(n, q)) if not isinstance(seed, np.random.RandomState) \
+        else seed.normal(size=(n, q))
+    Om = torch.as_tensor(omega).to(M.device)
+    Xt = torch.empty((m, k), dtype=torch.float64, device=M.device)
+    sig = torch.empty(k, dtype=torch.float64, device=M.device)
+    vt = torch.empty((k, n), dtype=torch.float64, device=M.device)
+    with torch.cuda.device(M.device):
+        _lib.check(lib.mused_svd_reduce(M.data_ptr(), dt, m, n, M.stride(0), Om.data_ptr(), q, k, int(n_iter),
+                                        Xt.data_ptr(), k, sig.data_ptr(), vt.data_ptr(), n,
+                                        torch.cuda.current_stream().cuda_stream))
+    out = Xt.cpu().numpy()
+    return (out, sig.cpu().numpy(), vt.cpu().numpy()) if return_model else out
+
+
 def contingency(prev_clusters, new_clusters, P, Q, *, device="cuda:0"):
     """counts[p, q] = #{i: prev[i] == p and new[i] == q} (matrix_operations.py:169-172)."""
     lib = _lib.load()

@@ -1,4 +1,5 @@
-"""The SWFDMC window loop of /root/reference/main.py:25-119 on the device operators.
+"""The SWFDMC window loop of /root/reference/main.py:25-119 on the device operators (and, with
+``approach="sSVDMC"``, the reference's per-window TruncatedSVD baseline, main.py:77-79, on the same operators).
 
 Same steps, same order, same arguments as ``process_streaming_data(approach="SWFDMC")``:
 per full window -- one kNN adjacency per modality (create_adjacency_matrix, :44-49), OR-fusion
@@ -19,8 +20,10 @@ from .swfd import SeqBasedSWFD
 
 def process_streaming_data(data_modalities, modality_types, complete_true_labels, *, window_size=2000,
                            reduced_dim=50, k_basis=50, seed=0, step_window_ratio=1, schedule="reference",
-                           device="cuda:0", kmeans="sklearn"):
+                           device="cuda:0", kmeans="sklearn", approach="SWFDMC"):
     """Returns (all_clusters, all_true_labels, per-window list of reduced matrices)."""
+    if approach not in ("SWFDMC", "sSVDMC"):
+        raise ValueError("approach must be SWFDMC or sSVDMC (the other baselines of main.py are host sklearn code)")
     subset_size = len(complete_true_labels)
     window, all_clusters, all_true, reduced = [], [], [], []
     swfd, prev_clusters = None, None
@@ -36,16 +39,19 @@ def process_streaming_data(data_modalities, modality_types, complete_true_labels
             # main.py:44-56: one uint8 W x W matrix on the device, every modality's top-k kernel ORs into it
             fused = mo.fused_adjacency([np.asarray(m[lo:i + 1]) for m in data_modalities], modality_types,
                                        k_basis=k_basis, device=device)
-            if swfd is None:                                                                  # main.py:60-62
-                max_norm = float(fused.sum(dim=1, dtype=torch.int64).max().item())            # ||0/1 row||^2 = degree
-                swfd = SeqBasedSWFD(N=window_size, R=max_norm, d=fused.shape[1], sketch_dim=reduced_dim,
-                                    schedule=schedule,
-                                    device=int(str(device).split(":")[-1]) if ":" in str(device) else 0)
-            swfd.fit(fused)                                   # main.py:65-67, the W uint8 rows in one call, device-resident
-            red = swfd.get()[0]                               # main.py:70
-            red = np.asarray(red.cpu() if hasattr(red, "cpu") else red)
-            if red.shape[0] != window_size:                   # main.py:73-76
-                red = red.T
+            if approach == "sSVDMC":                          # main.py:77-79: randomized TruncatedSVD of this window alone
+                red = mo.perform_svd_reduction(fused, reduced_dim, seed, device=device)
+            else:
+                if swfd is None:                                                                  # main.py:60-62
+                    max_norm = float(fused.sum(dim=1, dtype=torch.int64).max().item())            # ||0/1 row||^2 = degree
+                    swfd = SeqBasedSWFD(N=window_size, R=max_norm, d=fused.shape[1], sketch_dim=reduced_dim,
+                                        schedule=schedule,
+                                        device=int(str(device).split(":")[-1]) if ":" in str(device) else 0)
+                swfd.fit(fused)                                   # main.py:65-67, the W uint8 rows in one call, device-resident
+                red = swfd.get()[0]                               # main.py:70
+                red = np.asarray(red.cpu() if hasattr(red, "cpu") else red)
+                if red.shape[0] != window_size:                   # main.py:73-76
+                    red = red.T
             reduced.append(red)
             clusters = mo.perform_clustering(red, n_clusters, seed, device=device, engine=kmeans)   # main.py:97
             clusters = mo.match_clusters(prev_clusters, clusters, method="hungarian", min_overlap=3,
