@@ -129,6 +129,15 @@ int mused_swfd_size(mused_swfd_t* h, int64_t* n);
 /* Rows consumed so far (SeqBasedSWFD.time). */
 int mused_swfd_time(mused_swfd_t* h, uint64_t* t);
 
+/* Checkpoint / resume of a sketch ("state_dict"; the reference keeps its state in Python objects and has no
+ * counterpart, SURVEY.md section 5 lists it as an optional next item): the handle's persistent device buffers and
+ * host counters as one HOST blob of mused_swfd_state_size bytes.  Both schedules; with schedule = BATCHED the rows
+ * of the open chunk are part of the state.  A blob loads only into a handle created with the same configuration
+ * (sizes are checked before anything is overwritten: MUSED_ERR_ARG otherwise).  save / load synchronise the device. */
+int mused_swfd_state_size(mused_swfd_t* h, int64_t* bytes);
+int mused_swfd_state_save(mused_swfd_t* h, void* buf, int64_t cap);
+int mused_swfd_state_load(mused_swfd_t* h, const void* buf, int64_t bytes);
+
 /* Introspection for the differential tests: per FD instance (2 per level,
  * index 2*level + side, side 0 = the reference's current `fd`, 1 = `fd_aux`)
  * energy, delta, pending rows, last_dump_time, queue length, flush/dump counts.

@@ -249,7 +249,7 @@ struct BEngine {
     long long ahead = 0;              // rows staged beyond the open chunk (inside one fit() call)
     QueryScratch Q;
     double *o_sketch = nullptr, *o_vt = nullptr, *o_s2 = nullptr, *o_delta = nullptr;
-    std::vector<void*> allocs;
+    std::vector<StateAlloc> allocs;   // every device allocation; .state = part of the checkpoint (mused_swfd_state_*)
     cudaStream_t last_stream = nullptr;   // stream of the last fit(): size / debug read the slots behind it
     // column-sharded mode: this engine holds the columns of ONE rank; the two exchanges of a chunk
     // (||x||^2 of the rows, the Gram) are NCCL allreduces posted on the engine's stream from here
@@ -266,7 +266,7 @@ struct BEngine {
     long long timed_chunks = 0, timed_rows = 0;
 
     template <class T>
-    int alloc(T** p, size_t count) {
+    int alloc(T** p, size_t count, bool state = true) {
         void* q = nullptr;
         cudaError_t e = cudaMalloc(&q, count * sizeof(T));
         if (e != cudaSuccess) {
@@ -275,7 +275,7 @@ struct BEngine {
         }
         e = cudaMemset(q, 0, count * sizeof(T));
         if (e != cudaSuccess) { set_error("cudaMemset failed: %s", cudaGetErrorString(e)); return MUSED_ERR_CUDA; }
-        allocs.push_back(q);
+        allocs.push_back(StateAlloc{q, count * sizeof(T), state});
         *p = (T*)q;
         return 0;
     }
@@ -283,7 +283,7 @@ struct BEngine {
         if (comm && nccl_api().ok()) nccl_api().CommDestroy(comm);
         for (int k = 0; k < 5; ++k)
             for (cudaEvent_t e : ev[k]) cudaEventDestroy(e);
-        for (void* p : allocs) cudaFree(p);
+        for (const StateAlloc& a : allocs) cudaFree(a.p);
     }
     void mark(int k, cudaStream_t st) {
         if (!timing) return;
@@ -363,6 +363,7 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     D.KS = KS;
     int rc = 0;
 #define A_(p, n) if ((rc = E->alloc(&(p), (n))) != 0) { delete E; return rc; }
+#define S_(p, n) if ((rc = E->alloc(&(p), (n), false)) != 0) { delete E; return rc; }   /* scratch: not checkpointed */
     const size_t Sa = (size_t)std::max(S, 1);
     A_(D.slots, Sa);
     A_(D.skhi, Sa * 2 * ell * d);
@@ -374,11 +375,11 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     A_(D.norm2, (size_t)n_streams * D.xrows);
     D.x0 = 0;
     A_(D.mask, Sa * ell);
-    A_(D.Gp, Sa * KS * D.n2 * D.n2);
-    A_(D.G, Sa * D.n2 * D.n2);
-    A_(D.Gs, Sa * D.n2 * D.n2);
-    A_(D.Thi, Sa * ell * D.n2 + 128 * D.n2);   // + slack: the 128-row T box of the last instance
-    A_(D.Tlo, Sa * ell * D.n2 + 128 * D.n2);
+    S_(D.Gp, Sa * KS * D.n2 * D.n2);
+    S_(D.G, Sa * D.n2 * D.n2);
+    S_(D.Gs, Sa * D.n2 * D.n2);
+    S_(D.Thi, Sa * ell * D.n2 + 128 * D.n2);   // + slack: the 128-row T box of the last instance
+    S_(D.Tlo, Sa * ell * D.n2 + 128 * D.n2);
     A_(D.s2, Sa * ell);
     A_(D.dump_slot, Sa * ell);
     A_(D.raw_list, Sa * 2 * ell);
@@ -387,31 +388,32 @@ int bengine_create(BEngine** out, long long N, long long d, long long ell, doubl
     A_(D.ringT, Sa * D.capn);
     E->raw_rows = std::max<long long>(ell, std::min<long long>(8192, (64ll << 20) / (d * 8 * n_streams)));
     E->raw_bytes = (size_t)n_streams * E->raw_rows * d * 8;
-    A_(E->raw, E->raw_bytes);
+    S_(E->raw, E->raw_bytes);
     QueryScratch& Q = E->Q;
     Q.ng_max = D.ell + D.capn + 1;
     Q.ng_max += Q.ng_max & 1;
     Q.lda = Q.ng_max;
     Q.rel_thr = 1e-11;     // the fp32-product Grams upstream carry ~1e-6; 1e-11 leaves eigenvalues exact to ~1e-20
-    A_(Q.M, (size_t)Q.ng_max * d);
-    A_(Q.G, (size_t)Q.lda * Q.lda);
-    A_(Q.Vq, (size_t)Q.lda * Q.lda);
-    A_(Q.cs, (size_t)Q.ng_max);
+    S_(Q.M, (size_t)Q.ng_max * d);
+    S_(Q.G, (size_t)Q.lda * Q.lda);
+    S_(Q.Vq, (size_t)Q.lda * Q.lda);
+    S_(Q.cs, (size_t)Q.ng_max);
     Q.plan_big();
-    A_(Q.eval, (size_t)Q.npad_max);
-    A_(Q.perm, (size_t)Q.npad_max);
-    A_(Q.lam, (size_t)Q.npad_max);
-    A_(Q.VT, (size_t)Q.npad_max * Q.ldt);
-    A_(Q.mailL, Q.mail_count);
-    A_(Q.mailR, Q.mail_count);
-    A_(Q.sync, (size_t)QSYNC_WORDS);
-    A_(Q.counters, 64);
-    A_(Q.scr, 8);
-    A_(E->o_sketch, (size_t)ell * d);
-    A_(E->o_vt, (size_t)ell * d);
-    A_(E->o_s2, (size_t)ell);
-    A_(E->o_delta, 1);
+    S_(Q.eval, (size_t)Q.npad_max);
+    S_(Q.perm, (size_t)Q.npad_max);
+    S_(Q.lam, (size_t)Q.npad_max);
+    S_(Q.VT, (size_t)Q.npad_max * Q.ldt);
+    S_(Q.mailL, Q.mail_count);
+    S_(Q.mailR, Q.mail_count);
+    S_(Q.sync, (size_t)QSYNC_WORDS);
+    S_(Q.counters, 64);
+    S_(Q.scr, 8);
+    S_(E->o_sketch, (size_t)ell * d);
+    S_(E->o_vt, (size_t)ell * d);
+    S_(E->o_s2, (size_t)ell);
+    S_(E->o_delta, 1);
 #undef A_
+#undef S_
     std::vector<BSlot> init(Sa);
     memset(init.data(), 0, sizeof(BSlot) * Sa);
     for (int s = 0; s < S; ++s) {
@@ -774,6 +776,88 @@ int bengine_fit(BEngine* Ep, const void* rows, long long n_rows, long long ld, l
 }
 
 int bengine_streams(BEngine* E) { return E->K; }
+long long state_blob_bytes(const std::vector<StateAlloc>& a) {
+    long long n = (long long)sizeof(StateHeader);
+    for (const StateAlloc& x : a)
+        if (x.state) n += 8 + (long long)x.bytes;
+    return n;
+}
+
+int state_blob_save(unsigned kind, const unsigned long long (&host)[6], const std::vector<StateAlloc>& a, void* buf, long long cap) {
+    MUSED_REQUIRE(buf && cap >= state_blob_bytes(a), "state buffer of %lld bytes is too small (need %lld)", cap, state_blob_bytes(a));
+    MUSED_CUDA(cudaDeviceSynchronize());
+    unsigned char* o = (unsigned char*)buf;
+    StateHeader h;
+    h.magic = STATE_MAGIC;
+    h.kind = kind;
+    h.n_allocs = 0;
+    for (const StateAlloc& x : a) h.n_allocs += x.state ? 1u : 0u;
+    memcpy(h.host, host, sizeof(h.host));
+    memcpy(o, &h, sizeof(h));
+    o += sizeof(h);
+    for (const StateAlloc& x : a) {
+        if (!x.state) continue;
+        const unsigned long long b = x.bytes;
+        memcpy(o, &b, 8);
+        o += 8;
+        MUSED_CUDA(cudaMemcpy(o, x.p, x.bytes, cudaMemcpyDeviceToHost));
+        o += x.bytes;
+    }
+    return 0;
+}
+
+int state_blob_load(unsigned kind, unsigned long long (&host)[6], const std::vector<StateAlloc>& a, const void* buf, long long bytes) {
+    MUSED_REQUIRE(buf && bytes >= (long long)sizeof(StateHeader), "state blob too short");
+    const unsigned char* o = (const unsigned char*)buf;
+    StateHeader h;
+    memcpy(&h, o, sizeof(h));
+    MUSED_REQUIRE(h.magic == STATE_MAGIC, "not a mused_b200 state blob");
+    MUSED_REQUIRE(h.kind == kind, "state blob of the other schedule (saved %u, this handle %u)", h.kind, kind);
+    MUSED_REQUIRE(bytes == state_blob_bytes(a), "state blob of %lld bytes does not fit this handle's configuration (%lld bytes)",
+                  bytes, state_blob_bytes(a));
+    // first pass: every size must match before anything is overwritten
+    const unsigned char* q = o + sizeof(h);
+    unsigned n = 0;
+    for (const StateAlloc& x : a) {
+        if (!x.state) continue;
+        unsigned long long b;
+        memcpy(&b, q, 8);
+        MUSED_REQUIRE(b == x.bytes, "state blob buffer %u has %llu bytes, this handle's has %zu: another configuration", n, b, x.bytes);
+        q += 8 + x.bytes;
+        ++n;
+    }
+    MUSED_REQUIRE(n == h.n_allocs, "state blob holds %u buffers, this handle %u", h.n_allocs, n);
+    MUSED_CUDA(cudaDeviceSynchronize());
+    q = o + sizeof(h);
+    for (const StateAlloc& x : a) {
+        if (!x.state) continue;
+        q += 8;
+        MUSED_CUDA(cudaMemcpy(x.p, q, x.bytes, cudaMemcpyHostToDevice));
+        q += x.bytes;
+    }
+    memcpy(host, h.host, sizeof(h.host));
+    return 0;
+}
+
+// checkpoint of the batched engine: the open chunk (staged, not yet folded rows) is part of the state
+int bengine_state(BEngine* E, int op, void* buf, long long cap, long long* bytes) {
+    MUSED_CUDA(cudaSetDevice(E->device));
+    if (bytes) *bytes = state_blob_bytes(E->allocs);
+    if (op == 0) return 0;
+    unsigned long long host[6] = {E->time, E->done, (unsigned long long)E->pend, (unsigned long long)E->ahead,
+                                  (unsigned long long)E->D.x0, 0ull};
+    if (op == 1) return state_blob_save(1u, host, E->allocs, buf, cap);
+    MUSED_REQUIRE(!E->comm, "load_state on a handle attached to a communicator: load before attaching");
+    if (int rc = state_blob_load(1u, host, E->allocs, buf, cap)) return rc;
+    E->time = host[0];
+    E->done = host[1];
+    E->pend = (int)host[2];
+    E->ahead = (long long)host[3];
+    E->D.x0 = (int)host[4];
+    E->q_ng = 0;
+    return 0;
+}
+
 unsigned long long bengine_time(BEngine* E) { return E->time; }
 int bengine_qcap(BEngine* E) { return E->D.capn; }
 

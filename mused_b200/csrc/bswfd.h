@@ -1,6 +1,7 @@
 // Batched-schedule SWFD engine: device state and the host entry points the C ABI
 // (swfd_engine.cu) forwards to.
 #pragma once
+#include <vector>
 #include "common.cuh"
 #include "eig_common.cuh"
 
@@ -77,6 +78,21 @@ int bengine_get_finish(BEngine* E, double* sketch, double* sigma2, double* vt, d
 int nccl_unique_id(void* out, long long cap, long long* n_bytes, const char* nccl_path);
 int bengine_attach_comm(BEngine* E, const void* unique_id, long long id_bytes, int rank, int nranks, const char* nccl_path);
 int bengine_comm_stats(BEngine* E, unsigned long long* n, unsigned long long* bytes);
+
+// ---- state_dict support (optional checkpoint / resume; the reference has none) -----------------------
+// A handle's state = its persistent device allocations, byte for byte, + a few host scalars.  The blob can only be
+// loaded into a handle created with the same configuration (same allocation list): sizes are checked.
+struct StateAlloc { void* p; size_t bytes; bool state; };
+struct StateHeader {
+    unsigned long long magic;          // "MUSEDST1"
+    unsigned int kind, n_allocs;       // 0 = reference schedule, 1 = batched
+    unsigned long long host[6];
+};
+constexpr unsigned long long STATE_MAGIC = 0x315453444553554dull;
+long long state_blob_bytes(const std::vector<StateAlloc>& a);
+int state_blob_save(unsigned kind, const unsigned long long (&host)[6], const std::vector<StateAlloc>& a, void* buf, long long cap);
+int state_blob_load(unsigned kind, unsigned long long (&host)[6], const std::vector<StateAlloc>& a, const void* buf, long long bytes);
+int bengine_state(BEngine* E, int op, void* buf, long long cap, long long* bytes);   // op 0 size, 1 save, 2 load
 
 // Shared query tail (swfd_engine.cu): top-l shrink of the float64 stack M (ng x d).
 struct QueryScratch {

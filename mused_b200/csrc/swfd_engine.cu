@@ -473,7 +473,7 @@ struct Engine {
     QueryScratch Q;
     double *o_sketch = nullptr, *o_vt = nullptr, *o_s2 = nullptr, *o_delta = nullptr;
     int* o_flag = nullptr;
-    std::vector<void*> allocs;
+    std::vector<StateAlloc> allocs;   // every device allocation; .state = part of the checkpoint (mused_swfd_state_*)
     int sm_count = 148;
     bool timing = false;
     std::vector<cudaEvent_t> ev;   // start/stop pairs around k_swfd_rows (MODE_SEQ/FD)
@@ -481,7 +481,7 @@ struct Engine {
     long long timed_launches = 0, timed_rows = 0;
 
     template <class T>
-    int alloc(T** p, size_t count) {
+    int alloc(T** p, size_t count, bool state = true) {
         void* q = nullptr;
         cudaError_t e = cudaMalloc(&q, count * sizeof(T));
         if (e != cudaSuccess) {
@@ -490,12 +490,12 @@ struct Engine {
         }
         e = cudaMemset(q, 0, count * sizeof(T));
         if (e != cudaSuccess) { set_error("cudaMemset failed: %s", cudaGetErrorString(e)); return MUSED_ERR_CUDA; }
-        allocs.push_back(q);
+        allocs.push_back(StateAlloc{q, count * sizeof(T), state});
         *p = (T*)q;
         return 0;
     }
     ~Engine() {
-        for (void* p : allocs) cudaFree(p);
+        for (const StateAlloc& a : allocs) cudaFree(a.p);
     }
 };
 
@@ -574,6 +574,7 @@ static int engine_create(Engine** out, long long N, long long d, long long ell, 
     E->chunk_rows = chunk_rows;
     int rc = 0;
 #define A_(p, n) if ((rc = E->alloc(&(p), (n))) != 0) { delete E; return rc; }
+#define S_(p, n) if ((rc = E->alloc(&(p), (n), false)) != 0) { delete E; return rc; }   /* scratch: not checkpointed */
     if (S > 0) {
         A_(D.slots, (size_t)S);
         A_(D.R, (size_t)S * 2 * D.nmax * d);
@@ -587,35 +588,36 @@ static int engine_create(Engine** out, long long N, long long d, long long ell, 
         A_(D.ringT, (size_t)S * D.capn);
     }
     E->raw_bytes = (size_t)chunk_rows * d * 8;
-    A_(E->raw, E->raw_bytes);
-    A_(E->stage, (size_t)chunk_rows * d);
-    A_(E->norm2, (size_t)chunk_rows);
-    A_(E->times_dev, (size_t)chunk_rows);
+    S_(E->raw, E->raw_bytes);
+    S_(E->stage, (size_t)chunk_rows * d);
+    S_(E->norm2, (size_t)chunk_rows);
+    S_(E->times_dev, (size_t)chunk_rows);
     QueryScratch& Q = E->Q;
     Q.ng_max = D.ell + D.capn + 1;
     Q.ng_max += Q.ng_max & 1;
     Q.lda = Q.ng_max;
     if (!fd_only) {
-        A_(Q.M, (size_t)Q.ng_max * d);
-        A_(Q.G, (size_t)Q.lda * Q.lda);
-        A_(Q.Vq, (size_t)Q.lda * Q.lda);
-        A_(Q.cs, (size_t)Q.ng_max);
+        S_(Q.M, (size_t)Q.ng_max * d);
+        S_(Q.G, (size_t)Q.lda * Q.lda);
+        S_(Q.Vq, (size_t)Q.lda * Q.lda);
+        S_(Q.cs, (size_t)Q.ng_max);
         Q.plan_big();
-        A_(Q.eval, (size_t)Q.npad_max);
-        A_(Q.perm, (size_t)Q.npad_max);
-        A_(Q.lam, (size_t)Q.npad_max);
-        A_(Q.VT, (size_t)Q.npad_max * Q.ldt);
-        A_(Q.mailL, Q.mail_count);
-        A_(Q.mailR, Q.mail_count);
-        A_(Q.sync, (size_t)QSYNC_WORDS);
-        A_(Q.counters, 64);
-        A_(Q.scr, 8);
+        S_(Q.eval, (size_t)Q.npad_max);
+        S_(Q.perm, (size_t)Q.npad_max);
+        S_(Q.lam, (size_t)Q.npad_max);
+        S_(Q.VT, (size_t)Q.npad_max * Q.ldt);
+        S_(Q.mailL, Q.mail_count);
+        S_(Q.mailR, Q.mail_count);
+        S_(Q.sync, (size_t)QSYNC_WORDS);
+        S_(Q.counters, 64);
+        S_(Q.scr, 8);
     }
-    A_(E->o_sketch, (size_t)ell * d);
-    A_(E->o_vt, (size_t)ell * d);
-    A_(E->o_s2, (size_t)ell);
-    A_(E->o_delta, 1);
-    A_(E->o_flag, 1);
+    S_(E->o_sketch, (size_t)ell * d);
+    S_(E->o_vt, (size_t)ell * d);
+    S_(E->o_s2, (size_t)ell);
+    S_(E->o_delta, 1);
+    S_(E->o_flag, 1);
+#undef S_
 #undef A_
     std::vector<Slot> init(S);
     memset(init.data(), 0, sizeof(Slot) * S);
@@ -893,6 +895,33 @@ int mused_swfd_fit_timed(mused_swfd_t* h, const void* rows, int64_t n_rows, int6
 int mused_swfd_time(mused_swfd_t* h, uint64_t* t) {
     MUSED_REQUIRE(h && t, "NULL argument");
     *t = h->B ? bengine_time(h->B) : h->E->time;
+    return 0;
+}
+// Checkpoint / resume (SURVEY 5 "state_dict"; the reference keeps its state in Python objects only and has no
+// counterpart): the handle's persistent device buffers + host counters as one host blob.  A blob loads only into
+// a handle created with the same configuration.
+int mused_swfd_state_size(mused_swfd_t* h, int64_t* bytes) {
+    MUSED_REQUIRE(h && bytes, "NULL argument");
+    if (h->B) { long long b = 0; int rc = bengine_state(h->B, 0, nullptr, 0, &b); *bytes = b; return rc; }
+    *bytes = state_blob_bytes(h->E->allocs);
+    return 0;
+}
+int mused_swfd_state_save(mused_swfd_t* h, void* buf, int64_t cap) {
+    MUSED_REQUIRE(h && buf, "NULL argument");
+    if (h->B) return bengine_state(h->B, 1, buf, cap, nullptr);
+    Engine& E = *h->E;
+    MUSED_CUDA(cudaSetDevice(E.device));
+    const unsigned long long host[6] = {E.time, 0ull, 0ull, 0ull, 0ull, 0ull};
+    return state_blob_save(0u, host, E.allocs, buf, cap);
+}
+int mused_swfd_state_load(mused_swfd_t* h, const void* buf, int64_t bytes) {
+    MUSED_REQUIRE(h && buf, "NULL argument");
+    if (h->B) return bengine_state(h->B, 2, const_cast<void*>(buf), bytes, nullptr);
+    Engine& E = *h->E;
+    MUSED_CUDA(cudaSetDevice(E.device));
+    unsigned long long host[6] = {0, 0, 0, 0, 0, 0};
+    if (int rc = state_blob_load(0u, host, E.allocs, buf, bytes)) return rc;
+    E.time = host[0];
     return 0;
 }
 int mused_swfd_profile(mused_swfd_t* h, uint64_t* cycles, int64_t n_inst_cap) {

@@ -60,6 +60,32 @@ class SeqBasedSWFD:
         _lib.check(lib.mused_swfd_create(C.byref(self._h), C.byref(cfg)))
         self._lib = lib
         self._device = int(device)
+        self._cfg_key = dict(N=int(N), d=self.d, sketch_dim=self.sketch_dim, beta=float(beta), thresholds=list(thr),
+                             schedule=schedule, batch_rows=int(batch_rows), n_streams=int(n_streams),
+                             cluster=int(cluster), chunk_rows=int(chunk_rows))
+
+    # -- checkpoint / resume (no counterpart in the reference: SURVEY.md section 5 "state_dict") ---------------
+    def state_dict(self):
+        """The sketch as a picklable dict: the configuration it was built with and one uint8 array holding the
+        engine's device state (C ABI ``mused_swfd_state_save``).  ``load_state_dict`` on a sketch constructed with
+        the same arguments continues the stream exactly where this one stands (bit-identical results)."""
+        n = C.c_int64(0)
+        _lib.check(self._lib.mused_swfd_state_size(self._h, C.byref(n)))
+        blob = np.empty(int(n.value), dtype=np.uint8)
+        _lib.check(self._lib.mused_swfd_state_save(self._h, blob.ctypes.data, int(n.value)))
+        return dict(format="mused_b200.swfd/1", cfg=dict(self._cfg_key), blob=blob,
+                    last_level=getattr(self, "last_level", None))
+
+    def load_state_dict(self, state):
+        if state.get("format") != "mused_b200.swfd/1":
+            raise ValueError("not a mused_b200 sketch state")
+        if state["cfg"] != self._cfg_key:
+            diff = {k: (state["cfg"].get(k), v) for k, v in self._cfg_key.items() if state["cfg"].get(k) != v}
+            raise ValueError("state was saved from a sketch with another configuration: %r" % (diff,))
+        blob = np.ascontiguousarray(np.asarray(state["blob"], dtype=np.uint8))
+        _lib.check(self._lib.mused_swfd_state_load(self._h, blob.ctypes.data, int(blob.size)))
+        if state.get("last_level") is not None:
+            self.last_level = state["last_level"]
 
     # -- reference API -----------------------------------------------------
     def fit(self, X):
