@@ -64,13 +64,15 @@ def main():
                         rec[key] = None
             summary.append(rec)
             base = re.sub(r"<.*", "", name)
+            if re.match(r"k_assign_tc<\d+, \d+, 1>", name):
+                base = "k_assign_tc_screen"
             if (ri == 0 or append) and base not in dominant:
                 d = {"dram_bytes_per_launch": (rec.get("dram_read") or 0) + (rec.get("dram_write") or 0),
                      "duration_ms_under_ncu": 1e3 * rec["duration"], "issue_active_pct": rec.get("issue_active_pct"),
                      "tensor_pipe_pct": rec.get("tensor_pipe_pct"), "warp_instructions": rec.get("warp_instructions"),
                      "registers": rec.get("registers"),
                      "source": "profiles/r02_ncu_full_summary.csv (%s, --cache-control none)" % os.path.basename(path)}
-                if base == "k_eig_jacobi":
+                if base in ("k_eig_jacobi", "k_swfd_rows", "k_assign_tc_screen"):
                     st = {h[len("smsp__average_warps_issue_stalled_"):-len("_per_issue_active.ratio")]:
                           float(r[ix[h]].replace(",", "")) for h in stall}
                     d["stall_cycles_per_issued_instruction"] = {k: round(v, 3) for k, v in sorted(st.items(), key=lambda kv: -kv[1]) if v >= 0.01}
