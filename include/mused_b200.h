@@ -280,6 +280,19 @@ int mused_topk_adjacency_static(const float* feats, int64_t W, int64_t f, int64_
 int mused_topk_adjacency_f64(const double* feats, int64_t W, int64_t f, int64_t ld, int metric,
                              int64_t k, uint8_t* adj, void* stream);
 
+/* The two string modalities of create_adjacency_matrix on integer ids (the strings themselves are mapped to ids by
+ * the host wrapper -- dictionaries of user names / tag tokens are host string processing):
+ *  - "username" (matrix_operations.py:55-72): group[i] = id of row i's user name, < 0 for an empty name; every
+ *    pair of distinct rows with the same id gets an edge in both directions.
+ *  - "tags" (:74-89 with jaccard_similarity :245-248): row i's tag set is the sorted unique ids
+ *    ids[offsets[i] .. offsets[i+1]); similarity = |A & B| / |A u B| (float64 quotient, 0 if either set is empty,
+ *    -1 on the diagonal), every row gets edges to its k most similar rows (ties -> lowest index; the reference's
+ *    np.argsort leaves the order inside ties to numpy's introsort).
+ * Device pointers; adj is the W x W uint8 accumulator (edges are OR-ed in). */
+int mused_group_adjacency(const int32_t* group, int64_t W, uint8_t* adj, void* stream);
+int mused_jaccard_topk_adjacency(const int32_t* offsets, const int32_t* ids, int64_t W, int64_t k, uint8_t* adj,
+                                 void* stream);
+
 /* Contingency table for match_clusters (matrix_operations.py:169-172):
  * counts[p * Q + q] = #{i : prev[i] == p and cur[i] == q}; labels outside
  * [0,P) x [0,Q) are ignored.  Device pointers. */

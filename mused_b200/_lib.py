@@ -50,6 +50,7 @@ SYMBOLS = [
     "mused_swfd_fit_streams", "mused_swfd_get_stream", "mused_swfd_size_stream", "mused_swfd_debug_stream",
     "mused_topk_adjacency_static", "mused_assign_pending", "mused_svd_reduce",
     "mused_swfd_state_size", "mused_swfd_state_save", "mused_swfd_state_load",
+    "mused_group_adjacency", "mused_jaccard_topk_adjacency",
 ]
 
 
@@ -106,6 +107,8 @@ def load():
     lib.mused_swfd_state_size.argtypes = [vp, C.POINTER(i64)]
     lib.mused_swfd_state_save.argtypes = [vp, vp, i64]
     lib.mused_swfd_state_load.argtypes = [vp, vp, i64]
+    lib.mused_group_adjacency.argtypes = [vp, i64, vp, vp]
+    lib.mused_jaccard_topk_adjacency.argtypes = [vp, vp, i64, i64, vp, vp]
     lib.mused_svd_reduce.argtypes = [vp, C.c_int, i64, i64, i64, vp, i32, i32, i32, vp, i64, vp, vp, i64, vp]
     lib.mused_assign_pending.argtypes = [C.POINTER(C.c_uint64)]
     lib.mused_topk_adjacency.argtypes = [vp, i64, i64, i64, C.c_int, i64, vp, vp]

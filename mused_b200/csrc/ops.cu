@@ -3,6 +3,7 @@
 //                         nearest reference code matrix_operations.py:106, :286-289)
 //   mused_topk_adjacency  kNN -> 0/1 adjacency, OR-fused (matrix_operations.py:101-141)
 //   mused_topk_adjacency_static  the same with file-scope device scratch (no allocation; W <= 1024)
+//   mused_group_adjacency / mused_jaccard_topk_adjacency  the username / tags branches (:55-89) on integer ids
 //   mused_contingency     overlap counts of match_clusters (matrix_operations.py:169-172)
 #include <float.h>
 #include <stdlib.h>
@@ -366,6 +367,43 @@ __global__ void __launch_bounds__(256) k_kmeans_stats(const float* __restrict__ 
     }
 }
 
+// "username" branch of create_adjacency_matrix (matrix_operations.py:55-72): rows with the same group id are
+// neighbours of each other.  group[i] < 0 = row without a user name (no edges).
+__global__ void __launch_bounds__(256) k_group_adjacency(const int* __restrict__ group, long long W,
+                                                         unsigned char* __restrict__ adj) {
+    for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < W * W; e += (long long)gridDim.x * 256) {
+        const long long i = e / W, j = e % W;
+        const int gi = group[i];
+        if (gi >= 0 && i != j && gi == group[j]) adj[e] = 1;
+    }
+}
+
+// "tags" branch (:74-89, jaccard_similarity :245-248): row i's tag set = sorted unique token ids
+// ids[offsets[i] .. offsets[i+1]).  S[i][j] = |A & B| / |A u B| as the float64 quotient of the two integers (the
+// reference's Python division), 0 when either set is empty, -1 on the diagonal (:88).
+__global__ void __launch_bounds__(256) k_jaccard_keys(const int* __restrict__ offsets, const int* __restrict__ ids,
+                                                      long long W, double* __restrict__ S) {
+    for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < W * W; e += (long long)gridDim.x * 256) {
+        const long long i = e / W, j = e % W;
+        double key;
+        if (i == j) key = -1.0;
+        else {
+            int a = offsets[i], b = offsets[j];
+            const int ae = offsets[i + 1], be = offsets[j + 1];
+            const int na = ae - a, nb = be - b;
+            int common = 0;
+            while (a < ae && b < be) {
+                const int x = ids[a], y = ids[b];
+                common += (x == y);
+                a += (x <= y);
+                b += (y <= x);
+            }
+            key = (na == 0 || nb == 0) ? 0.0 : (double)common / (double)(na + nb - common);
+        }
+        S[e] = key;
+    }
+}
+
 // Scratch comes from the stream-ordered pool; by default that pool hands its memory back to the
 // driver at every synchronisation, which makes the next cudaMallocAsync map fresh pages (slow and
 // erratic).  Keep the pages: one attribute on the device's default pool, set once per device.
@@ -623,6 +661,37 @@ int mused_topk_adjacency_f64(const double* feats, int64_t W, int64_t f, int64_t 
     MUSED_CUDA(cudaMallocAsync((void**)&S, sizeof(double) * (size_t)W * W, st));
     const int sms = sm_count_of_current();
     k_pair_keys_f64<<<(int)std::min<long long>((W * W + 255) / 256, 16ll * sms), 256, 0, st>>>(feats, W, f, ld, metric, S);
+    MUSED_CUDA(cudaGetLastError());
+    const size_t smem = (size_t)W * sizeof(double);
+    MUSED_CUDA(cudaFuncSetAttribute(k_topk_rows<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_topk_rows<double><<<(int)std::min<long long>(W, 8ll * sms), 256, smem, st>>>(S, W, k, adj);
+    MUSED_CUDA(cudaGetLastError());
+    MUSED_CUDA(cudaFreeAsync(S, st));
+    mused_count_launches(2);
+    return 0;
+}
+
+int mused_group_adjacency(const int32_t* group, int64_t W, uint8_t* adj, void* stream) {
+    MUSED_REQUIRE(W >= 1 && group && adj, "bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int grid = (int)std::min<long long>((W * W + 255) / 256, 16ll * sm_count_of_current());
+    k_group_adjacency<<<grid, 256, 0, st>>>(group, W, adj);
+    MUSED_CUDA(cudaGetLastError());
+    mused_count_launches(1);
+    return 0;
+}
+
+int mused_jaccard_topk_adjacency(const int32_t* offsets, const int32_t* ids, int64_t W, int64_t k, uint8_t* adj,
+                                 void* stream) {
+    MUSED_REQUIRE(W >= 1 && k >= 0 && offsets && adj, "bad argument");
+    MUSED_REQUIRE(W * 8 <= 200 * 1024, "window of %lld rows exceeds the per-row shared-memory select (max 25600)", (long long)W);
+    if (k == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    keep_pool_memory();
+    double* S = nullptr;
+    MUSED_CUDA(cudaMallocAsync((void**)&S, sizeof(double) * (size_t)W * W, st));
+    const int sms = sm_count_of_current();
+    k_jaccard_keys<<<(int)std::min<long long>((W * W + 255) / 256, 16ll * sms), 256, 0, st>>>(offsets, ids, W, S);
     MUSED_CUDA(cudaGetLastError());
     const size_t smem = (size_t)W * sizeof(double);
     MUSED_CUDA(cudaFuncSetAttribute(k_topk_rows<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

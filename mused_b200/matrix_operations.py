@@ -86,14 +86,65 @@ def topk_adjacency(features, k, *, metric="cosine", out=None, device="cuda:0"):
     return out
 
 
+STRING_MODALITIES = ("username", "tags")
+
+
+def _first_column(data):
+    a = np.asarray(data, dtype=object)
+    return a[:, 0] if a.ndim == 2 else a
+
+
+def _string_adjacency(data, modality_type, k_basis, out, device):
+    """The "username" (matrix_operations.py:55-72) and "tags" (:74-89) branches: strings -> integer ids on the
+    host (dictionaries), all pairwise work + top-k + edge writing on the device; edges are OR-ed into ``out``."""
+    lib = _lib.load()
+    col = _first_column(data)
+    W = len(col)
+    valid = np.array([i for i in range(W) if not (isinstance(col[i], str) and col[i] == "")], dtype=np.int64)   # data[:, 0] != ''
+    if len(valid) == 0:
+        return out
+    nv = len(valid)
+    sub = out if nv == W else torch.zeros((nv, nv), dtype=torch.uint8, device=out.device)
+    with torch.cuda.device(out.device):
+        st = torch.cuda.current_stream().cuda_stream
+        if modality_type == "username":
+            ids, table = np.empty(nv, dtype=np.int32), {}
+            for r, i in enumerate(valid):
+                ids[r] = table.setdefault(col[i], len(table))
+            g = torch.as_tensor(ids).to(out.device)
+            _lib.check(lib.mused_group_adjacency(g.data_ptr(), nv, sub.data_ptr(), st))
+        else:
+            # set(tags): the characters of a string, the items of a list (:83)
+            table, rows = {}, []
+            for i in valid:
+                t = col[i]
+                rows.append(sorted({table.setdefault(tok, len(table)) for tok in t}) if t is not None and len(t) else [])
+            offs = np.zeros(nv + 1, dtype=np.int32)
+            offs[1:] = np.cumsum([len(r) for r in rows])
+            flat = np.fromiter((v for r in rows for v in r), dtype=np.int32, count=int(offs[-1]))
+            o = torch.as_tensor(offs).to(out.device)
+            f = torch.as_tensor(flat if len(flat) else np.zeros(1, dtype=np.int32)).to(out.device)
+            _lib.check(lib.mused_jaccard_topk_adjacency(o.data_ptr(), f.data_ptr(), nv, min(int(k_basis), nv),
+                                                        sub.data_ptr(), st))
+    if sub is not out:
+        idx = torch.as_tensor(valid, device=out.device)
+        out[idx[:, None], idx[None, :]] |= sub
+    return out
+
+
 def create_adjacency_matrix(data, modality_type, k_basis=50, *, device="cuda:0"):
-    """Dense numeric branches of matrix_operations.py:14-132 -> W x W float64 0/1 ndarray.
+    """create_adjacency_matrix of matrix_operations.py:14-132 -> W x W float64 0/1 ndarray.
 
     modality_type "location": (latitude, longitude) rows, haversine kNN, k = k_basis + 1;
     "time": (datetaken, dateupload) rows, |d taken| + |d upload|, k = 3 k_basis + 1;
     "text"/"cosine": rows are (TF-IDF or embedding) vectors, cosine top-(k_basis+1);
+    "username": rows of the same user name are neighbours; "tags": Jaccard top-k_basis of the tag sets;
     anything else: Euclidean kNN with k = k_basis (the reference's default branch).
     """
+    if modality_type in STRING_MODALITIES:
+        W = len(_first_column(data))
+        out = torch.zeros((W, W), dtype=torch.uint8, device=device)
+        return _string_adjacency(data, modality_type, k_basis, out, device).cpu().numpy().astype(np.float64)
     A = np.asarray(data, dtype=np.float64)
     W = A.shape[0]
     out = np.zeros((W, W))
@@ -123,6 +174,9 @@ def fused_adjacency(data_modalities, modality_types, k_basis=50, *, device="cuda
     W = len(data_modalities[0])
     fused = torch.zeros((W, W), dtype=torch.uint8, device=device)
     for m, t in zip(data_modalities, modality_types):
+        if t in STRING_MODALITIES:
+            _string_adjacency(m, t, k_basis, fused, device)
+            continue
         A = np.asarray(m, dtype=np.float64)
         valid, k, metric = _modality_plan(A, t, k_basis)
         if len(valid) == 0:

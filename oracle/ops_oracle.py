@@ -96,3 +96,53 @@ def contingency(prev, cur, P, Q):
         if 0 <= p < P and 0 <= q < Q:
             out[p, q] += 1
     return out
+
+
+def username_adjacency(col):
+    """matrix_operations.py:55-72 + writer :123-130: rows with the same non-empty user name are neighbours."""
+    W = len(col)
+    out = np.zeros((W, W))
+    valid = [i for i in range(W) if col[i] != ""]
+    groups = {}
+    for r, i in enumerate(valid):
+        groups.setdefault(col[i], []).append(r)
+    for r, i in enumerate(valid):
+        for q in groups[col[i]]:
+            if valid[q] != i:
+                out[i, valid[q]] = 1
+    return out
+
+
+def jaccard_matrix(col):
+    """:74-89 similarities of the valid rows (jaccard_similarity :245-248, -1 on the diagonal) and their indices."""
+    W = len(col)
+    valid = [i for i in range(W) if col[i] != ""]
+    sets = [set(col[i]) if col[i] else set() for i in valid]
+    n = len(valid)
+    S = np.zeros((n, n))
+    for a in range(n):
+        for b in range(n):
+            if a == b:
+                S[a, b] = -1
+            elif sets[a] and sets[b]:
+                S[a, b] = len(sets[a] & sets[b]) / len(sets[a] | sets[b])
+    return S, np.asarray(valid)
+
+
+def tags_adjacency(col, k):
+    """The tags branch with ties broken by the lowest index (np.argsort(kind="stable")); the reference's default
+    argsort leaves the order inside ties to numpy's introsort, so only rows whose k-th and (k+1)-th similarities
+    differ are determined by the reference itself.  Returns (adjacency, mask of such determined rows)."""
+    S, valid = jaccard_matrix(col)
+    W = len(col)
+    out = np.zeros((W, W))
+    determined = np.ones(W, dtype=bool)
+    for a in range(len(valid)):
+        order = np.argsort(-S[a], kind="stable")
+        top = order[:k]
+        if k < len(valid) and S[a, order[k - 1]] == S[a, order[k]]:
+            determined[valid[a]] = False
+        for b in top:
+            if valid[b] != valid[a]:
+                out[valid[a], valid[b]] = 1
+    return out, determined
