@@ -58,6 +58,9 @@ def parse():
                     help="batched: north_star's chunked tensor-core schedule (headline); "
                          "reference: the reference's per-row flush schedule")
     ap.add_argument("--no-refsched", action="store_true", help="skip the extra reference-schedule timing")
+    ap.add_argument("--config", type=int, default=1, choices=[1, 3],
+                    help="BASELINE.json configs[] index of the workload: 1 = the metric's own (d=1024, l=128, N=10k); "
+                         "3 = d=4096, l=256, N=100k (tensor-bound Gram / rotate; diagnostic line, device legs only)")
     return ap.parse_args()
 
 
@@ -525,8 +528,10 @@ def run_ours(args, rank, local_rank, world):
         if os.path.exists(pj):
             with open(pj) as f:
                 ncu = json.load(f)
-        kname = {"K1_stage": "k_bstage", "K5_book": "k_bbook", "K2_gram": "k_gram_tc",
+        kname = {"K1_stage": "k_bstage", "K5_book": "k_bbook", "K2_gram": "k_gram_tc" if ELL <= 128 else "k_gram_tiled",
                  "K3_eig": "k_eig_jacobi", "K4_rotate": "k_rotate_tc"}[dom]
+        if args.config != 1:
+            ncu = {}                                       # the committed ncu figures are of the configs[1] capture
         nk = ncu.get(kname, {})
         roofline = {"bound": "hbm", "kernel": kname,
                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -579,7 +584,7 @@ def run_ours(args, rank, local_rank, world):
            "last_timed_window_" + args.schedule: so.cov_error(A[(n_steps - 1) * WIN:n_steps * WIN].astype(np.float64),
                                                                main_res["sketch"])}
     fx = os.path.join(ROOT, "tests", "golden", "full_c1.npz")
-    if os.path.exists(fx):
+    if os.path.exists(fx) and args.config == 1:
         import hashlib
         from mused_b200 import synth
         g = np.load(fx)
@@ -627,10 +632,11 @@ def run_ours(args, rank, local_rank, world):
         "warmup": args.warmup, "ms_per_step": main_res["ms_total"] / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32 rows, 3xTF32 products, f32+f64 eigensolve"
         if args.schedule == "batched" else "f64", "data": "synthetic",
-        "config": {"workload": "SWFD d=1024 l=128 N=10000 low-rank+noise stream + cosine assign k=150 (configs[1])",
+        "config": {"workload": "SWFD d=%d l=%d N=%d low-rank+noise stream + cosine assign k=150 (configs[%d])"
+                               % (D, ELL, WIN, args.config),
                    "schedule": args.schedule, "levels": S // 2, "fd_instances": S, "rows_per_step": WIN,
-                   "l2": "each step streams a fresh 41 MB window (> nothing cached from the previous step's rows); "
-                         "FD state is meant to stay L2-resident",
+                   "l2": "each step streams a fresh %d MB window (> nothing cached from the previous step's rows); "
+                         "FD state is meant to stay L2-resident" % (WIN * D * 4 // 1000000),
                    "query_level": main_res["level"]},
         "clocks": main_res["clocks"], "multi_stream": multi, "get_ms_per_step": main_res["get_ms"],
         "cpu_batched_baseline": cpu_b, "sharded": sharded,
@@ -668,7 +674,19 @@ def run_ours(args, rank, local_rank, world):
 
 
 def main():
+    global D, ELL, WIN, R_BOUND, METRIC
     args = parse()
+    if args.config == 3:
+        # BASELINE.json configs[3]: the shape where K2 / K4 are tensor-bound; same step definition, device legs only
+        D, ELL, WIN, R_BOUND = 4096, 256, 100000, 128.0
+        METRIC = "stream rows/sec (SWFD update+assign) at d=4096,l=256 (configs[3]); cov-error vs reference"
+        args.no_refsched = args.no_sharded = True
+        args.streams = ""
+        args.no_cpu = args.no_cpu or args.cpu_rows == 0
+        if "--steps" not in sys.argv:
+            args.steps = 2
+        if "--warmup" not in sys.argv:
+            args.warmup = 3
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
