@@ -90,6 +90,21 @@ __global__ void k_assign_prep(const float* __restrict__ C, long long k, long lon
     }
 }
 
+// Third pass of the screening epilogue for warps that hold a row with more than three candidate keys: the bit mask of
+// the keys >= thr, one word per 32 centroids, written for the lanes that pass a destination.
+__device__ __noinline__ void screen_write_masks(uint32_t trow, int NP, int k, const float* cscale, float thr, uint32_t* dst) {
+    for (int c0 = 0; c0 < NP; c0 += 32) {
+        uint32_t v[32];
+        umma::tmem_ld32(trow + c0, v);
+        umma::tmem_ld_wait();
+        uint32_t m = 0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (c0 + j < k && __uint_as_float(v[j]) * cscale[c0 + j] >= thr) m |= 1u << j;
+        if (dst) dst[c0 >> 5] = m;
+    }
+}
+
 template <int MH, int NST, int PASSES = 3>
 __global__ void __launch_bounds__(Cfg<MH, NST, PASSES>::NTHREADS, Cfg<MH, NST, PASSES>::CTAS_PER_SM)
 k_assign_tc(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_chi,
@@ -265,18 +280,10 @@ k_assign_tc(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CU
                         }
                     }
                 }
-                if (__any_sync(0xffffffffu, cnt > 3)) {                          // rare: leave those rows' masks for the re-score
-                    for (int c0 = 0; c0 < NP; c0 += 32) {
-                        uint32_t v[32];
-                        umma::tmem_ld32(trow + c0, v);
-                        umma::tmem_ld_wait();
-                        uint32_t m = 0;
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (c0 + j < A.k && __uint_as_float(v[j]) * cscale[c0 + j] >= thr) m |= 1u << j;
-                        if (cnt > 3 && r < A.n) A.cmask[(size_t)r * A.nw + (c0 >> 5)] = m;
-                    }
-                }
+                // rare (more than three keys inside the bound): leave the rows' candidate masks for the re-score.  Kept
+                // out of line on purpose: inlined, this never-taken loop cost the hot epilogue 10 % (measured).
+                if (__any_sync(0xffffffffu, cnt > 3))
+                    screen_write_masks(trow, NP, A.k, cscale, thr, cnt > 3 && r < A.n ? A.cmask + (size_t)r * A.nw : nullptr);
                 umma::tc_fence_before();
                 umma::mbar_arrive(accfree);
                 if (r < A.n) {

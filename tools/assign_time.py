@@ -42,16 +42,18 @@ for n in [int(a) for a in sys.argv[1:]] or [10000, 1 << 20]:
                 out = mo.cosine_assign(X, C, tau, return_score=score)
             torch.cuda.synchronize()
             p0 = pending()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             reps = 20
-            e0.record()
-            for _ in range(reps):
+            evs = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+            evs[0].record()
+            for i in range(reps):
                 out = mo.cosine_assign(X, C, tau, return_score=score)
-            e1.record()
+                evs[i + 1].record()
             mhz = sm_mhz()                       # sampled while the last launches are still running
             torch.cuda.synchronize()
             lab = out[0] if score else out
-            ms = e0.elapsed_time(e1) / reps
+            per = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(reps))
+            ms = evs[0].elapsed_time(evs[reps]) / reps
+            spread = "min %.3f / median %.3f / max %.3f ms" % (per[0], per[reps // 2], per[-1])
             frac = (pending() - p0) / reps / n
             gb = (4.0 * n * d + 4.0 * k * d + 4.0 * n) / 1e9
             # check against a float64 torch reference on a slice
@@ -61,6 +63,6 @@ for n in [int(a) for a in sys.argv[1:]] or [10000, 1 << 20]:
             ref = torch.where(top2[:, 0] >= tau, S.argmax(1), torch.full((m,), -1, device="cuda"))
             sure = ((top2[:, 0] - top2[:, 1]) > 2e-5) & ((top2[:, 0] - tau).abs() > 2e-5)
             bad = int((lab[:m].long()[sure] != ref[sure]).sum())
-            print("n=%d %-6s %-22s %.3f ms  %.1f GB/s (%.1f%% of measured HBM peak)  re-scored %.2f%%  mismatches(sure rows)=%d/%d  SM %d MHz" %
+            print("n=%d %-6s %-22s %.3f ms  %.1f GB/s (%.1f%% of measured HBM peak)  re-scored %.2f%%  mismatches(sure rows)=%d/%d  SM %d MHz  [%s]" %
                   (n, kind, "3xTF32 (with score)" if score else "screen + re-score", ms, gb / ms * 1e3,
-                   100 * gb / ms * 1e3 / peak, 100 * frac, bad, int(sure.sum()), mhz), flush=True)
+                   100 * gb / ms * 1e3 / peak, 100 * frac, bad, int(sure.sum()), mhz, spread), flush=True)
