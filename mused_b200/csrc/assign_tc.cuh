@@ -47,7 +47,14 @@ struct Args {
     int nw;                            //            (read back by k_assign_rescore for rows with > 3 candidates)
 };
 
-constexpr float SCREEN_EPS = 1.1e-3f;  // >= 2^-10 (two RNA-rounded TF32 operands) + fp32 accumulation over d <= 64k
+#ifndef MUSED_ASSIGN_RAWX
+#define MUSED_ASSIGN_RAWX 1
+#endif
+// RAWX: the screening UMMA reads the fp32 rows of X as TMA delivered them (kind::tf32 uses the upper 19 bits of each
+// word: truncation, relative error < 2^-10) and the centroids rounded to nearest (<= 2^-11): |error of a cosine| <=
+// 1.5 * 2^-10 = 1.465e-3 by Cauchy-Schwarz.  Otherwise X is rounded to nearest in shared memory first (2^-10 in all).
+// SCREEN_EPS adds the fp32 accumulation slack (d <= 64k).
+constexpr float SCREEN_EPS = MUSED_ASSIGN_RAWX ? 1.6e-3f : 1.1e-3f;
 
 // pending codes left in labels[] by the screening kernel: label = -2 - (type << 24 | third << 16 | second << 8 | best)
 constexpr int PEND_ONE = 0, PEND_PAIR = 1, PEND_TRIPLE = 2, PEND_FULL = 3;
@@ -111,6 +118,7 @@ k_assign_tc(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CU
             const __grid_constant__ CUtensorMap tm_clo, Args A) {
     using CF = Cfg<MH, NST, PASSES>;
     constexpr int PL = CF::PLANES;
+    constexpr bool RAWX = PASSES == 1 && MUSED_ASSIGN_RAWX;     // no conversion of X in shared memory (see SCREEN_EPS)
     static_assert(PASSES == 1 || PASSES == 3, "one screening pass or the three passes of 3xTF32");
     extern __shared__ unsigned char smem_dyn[];
     unsigned char* base = (unsigned char*)(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
@@ -139,7 +147,7 @@ k_assign_tc(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CU
         for (int i = 0; i < NST; ++i) {
             umma::mbar_init(&full[i], 1);
             umma::mbar_init(&conv[i], MH * 128);
-            umma::mbar_init(&empty[i], 1);
+            umma::mbar_init(&empty[i], RAWX ? 1 + MH * 128 : 1);   // RAWX: the UMMA commit + every row's norm reader
         }
         umma::mbar_init(accum, 1);
         umma::mbar_init(accfree, MH * 128);
@@ -184,7 +192,7 @@ k_assign_tc(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CU
                 }
                 for (int kb = 0; kb < A.kblocks; ++kb, ++it) {
                     const uint32_t st = it % NST;
-                    umma::mbar_wait(&conv[st], (it / NST) & 1);
+                    umma::mbar_wait(RAWX ? &full[st] : &conv[st], (it / NST) & 1);
                     umma::tc_fence_after();
                     const uint32_t sb = umma::smem_u32(base + st * stage_bytes);
                     const uint32_t chi = sb + PL * a_bytes, clo = chi + c_bytes;
@@ -222,6 +230,19 @@ k_assign_tc(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CU
                 umma::mbar_wait(&full[st], (it / NST) & 1);
                 unsigned char* hi_row = base + st * stage_bytes + h * 128 * 128 + r_in * 128;
                 unsigned char* lo_row = hi_row + a_bytes;
+                if constexpr (RAWX) {
+                    // only the row's squared norm is needed: read the tile the UMMA is reading, release the stage
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int c = (lane + j) & 7;
+                        const float4 v = *reinterpret_cast<const float4*>(hi_row + c * 16);
+                        xn2 = fmaf(v.x, v.x, xn2);
+                        xn2 = fmaf(v.y, v.y, xn2);
+                        xn2 = fmaf(v.z, v.z, xn2);
+                        xn2 = fmaf(v.w, v.w, xn2);
+                    }
+                    umma::mbar_arrive(&empty[st]);
+                } else {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const int c = (lane + j) & 7;              // rotated chunk order: conflict-free quarter warps
@@ -240,6 +261,7 @@ k_assign_tc(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CU
                 }
                 umma::fence_proxy_async();                      // generic-proxy writes -> visible to the UMMA
                 umma::mbar_arrive(&conv[st]);
+                }
             }
             umma::mbar_wait(accum, t & 1);
             umma::tc_fence_after();
