@@ -108,6 +108,26 @@ def test_cosine_assign_screening_path_gives_the_exact_labels(kind, n, d, k, tau)
         assert frac < 0.02
 
 
+def test_screening_operand_semantics_of_the_tensor_core():
+    """assign_tc.cuh's error bound assumes that kind::tf32 UMMAs use the upper 19 bits of the fp32 words TMA
+    delivered (truncation, relative error < 2^-10) -- measured here.  Rows x = (1 + 2^-11 + 2^-13) * c with c = ones
+    (TF32-exact): truncation screens cos = 1 / (1 + 2^-11 + 2^-13) = 0.99939, round-to-nearest would give 1.00037.
+    With tau = 0.9983 and the bound 1.6e-3 the row is inside the threshold band (re-scored) only in the first case.
+    Either way the label is exact (cos = 1 >= tau)."""
+    import ctypes as C_
+    from mused_b200 import matrix_operations as mo, _lib
+    n, d = 512, 128
+    Cn = np.ones((1, d), dtype=np.float32)
+    X = np.full((n, d), 1.0 + 2.0 ** -11 + 2.0 ** -13, dtype=np.float32)
+    lib = _lib.load()
+    p0, p1 = C_.c_uint64(0), C_.c_uint64(0)
+    _lib.check(lib.mused_assign_pending(C_.byref(p0)))
+    lab = mo.cosine_assign(X, Cn, 0.9983).cpu().numpy()
+    _lib.check(lib.mused_assign_pending(C_.byref(p1)))
+    assert np.all(lab == 0)
+    assert p1.value - p0.value == n, "the tensor core did not truncate the fp32 operand: revisit SCREEN_EPS"
+
+
 @pytest.mark.parametrize("n,d,k", [(500, 50, 12), (64, 7, 3)])
 def test_l2_assign(n, d, k):
     from mused_b200 import matrix_operations as mo
