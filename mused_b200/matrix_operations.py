@@ -1,10 +1,11 @@
 """Numeric operators of /root/reference/matrix_operations.py on the B200.
 
 Same names and argument meaning as the reference for the functions main.py
-imports on the SWFDMC path; string modalities (username / tags / TF-IDF
-vocabulary building, matrix_operations.py:55-100) are host-side string
-processing and out of scope -- this module takes
-the dense feature matrices those branches produce.
+imports.  The string modalities "username" and "tags" (matrix_operations.py:55-89)
+map their strings to integer ids on the host (dictionaries) and do the pairwise
+work on the device; the TF-IDF vocabulary of the "text" branch (:91-100) stays
+host string processing (sklearn) -- its matrix goes through the device cosine
+top-k like any dense modality ("text" / "cosine").
 """
 from __future__ import annotations
 

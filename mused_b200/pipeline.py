@@ -6,8 +6,9 @@ per full window -- one kNN adjacency per modality (create_adjacency_matrix, :44-
 (:56), the rows of the fused W x W matrix through the sliding-window FD sketch (:60-67), ``get()``
 and the transpose fix-up (:70-76), KMeans (:97), Hungarian matching with the previous window
 (:106-110).  The fused adjacency stays on the device as one uint8 matrix from the top-k kernels to the sketch's
-row staging kernel (no per-modality W x W float64 matrices, no host round trip).  String modalities (username / tags / text) are host-side string processing in the
-reference and are not taken here.
+row staging kernel (no per-modality W x W float64 matrices, no host round trip).  The "username" and "tags"
+modalities are taken as string columns (ids on the host, pairwise work on the device); "text" takes the TF-IDF (or
+embedding) matrix the caller built.
 """
 from __future__ import annotations
 
