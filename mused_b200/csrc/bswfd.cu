@@ -92,6 +92,92 @@ __global__ void __launch_bounds__(256) k_bstage_v4(const float* __restrict__ in,
     }
 }
 
+// The same append with the rows staged by TMA (bulk copies): fp32 rows that are contiguous in memory (ld == d) and
+// fill the planes' rows (d_in == d).  CTAs of 4 warps (three per SM) loop over tiles of RT whole rows (<= 16 KB): a
+// 2-stage ring of bulk loads global -> shared (mbarrier); ONE WARP PER ROW splits the row in shared memory -- hi in
+// place, lo into a second buffer; lane-strided float4 in element order and the xor tree, i.e. exactly k_bstage_v4's
+// ||x||^2 -- and two bulk stores shared -> global per tile write the planes.  4 bytes read + 8 written per element,
+// all through the TMA engine; the SM only converts.
+constexpr int STMA_TILE_BYTES = 16 * 1024;
+constexpr int STMA_STAGES = 2;
+constexpr int STMA_NT = 128;
+__global__ void __launch_bounds__(STMA_NT, 3) k_bstage_tma(const float* __restrict__ in, long long stream_stride, long long xrows,
+                                                           long long d, long long m, int RT, int row_off,
+                                                           float* __restrict__ xhi, float* __restrict__ xlo,
+                                                           double* __restrict__ norm2) {
+    extern __shared__ __align__(128) unsigned char sraw[];
+    float* s_hi = reinterpret_cast<float*>(sraw);                                            // [STAGES][TILE] rows in, hi out
+    float* s_lo = reinterpret_cast<float*>(sraw + STMA_STAGES * STMA_TILE_BYTES);            // [STAGES][TILE]
+    uint64_t* full = reinterpret_cast<uint64_t*>(sraw + 2 * STMA_STAGES * STMA_TILE_BYTES);
+    const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+    // this CTA's tiles: blockIdx.x, blockIdx.x + gridDim.x, ... of ITS stream (grid.y = stream)
+    const long long stride = gridDim.x;
+    const long long t_begin = blockIdx.x, t_end = (m + RT - 1) / RT;
+    const float* src0 = in + (size_t)blockIdx.y * stream_stride;
+    const size_t dst_row0 = (size_t)blockIdx.y * xrows + row_off;
+    if (tid == 0) {
+        for (int i = 0; i < STMA_STAGES; ++i) umma::mbar_init(&full[i], 1);
+        umma::fence_mbar_init();
+    }
+    __syncthreads();
+    auto issue = [&](long long t, int st) {
+        const long long r0 = t * RT;
+        const uint32_t bytes = (uint32_t)(std::min<long long>(RT, m - r0) * d * 4);
+        umma::mbar_expect_tx(&full[st], bytes);
+        umma::bulk_load_1d(s_hi + (size_t)st * (STMA_TILE_BYTES / 4), src0 + (size_t)r0 * d, bytes, &full[st]);
+    };
+    if (tid == 0) {
+        long long t = t_begin;
+        for (int i = 0; i < STMA_STAGES && t < t_end; ++i, t += stride) issue(t, i);
+    }
+    int it = 0;
+    for (long long t = t_begin; t < t_end; t += stride, ++it) {
+        const int st = it % STMA_STAGES;
+        const long long r0 = t * RT;
+        const int rows = (int)std::min<long long>(RT, m - r0);
+        umma::mbar_wait(&full[st], (it / STMA_STAGES) & 1);
+        float* th = s_hi + (size_t)st * (STMA_TILE_BYTES / 4);
+        float* tl = s_lo + (size_t)st * (STMA_TILE_BYTES / 4);
+        for (int r = w; r < rows; r += STMA_NT / 32) {
+            float4* hi = reinterpret_cast<float4*>(th + (size_t)r * d);
+            float4* lo = reinterpret_cast<float4*>(tl + (size_t)r * d);
+            double acc = 0.0;
+            for (long long c = lane; c < d / 4; c += 32) {
+                const float4 v = hi[c];
+                float4 h, l;
+                umma::split_tf32(v.x, h.x, l.x);
+                umma::split_tf32(v.y, h.y, l.y);
+                umma::split_tf32(v.z, h.z, l.z);
+                umma::split_tf32(v.w, h.w, l.w);
+                hi[c] = h;
+                lo[c] = l;
+                acc = fma((double)v.x, (double)v.x, acc);
+                acc = fma((double)v.y, (double)v.y, acc);
+                acc = fma((double)v.z, (double)v.z, acc);
+                acc = fma((double)v.w, (double)v.w, acc);
+            }
+            acc = warp_sum(acc);
+            if (lane == 0) norm2[dst_row0 + r0 + r] = acc;
+        }
+        umma::fence_proxy_async();                 // the planes written above -> visible to the bulk stores
+        __syncthreads();
+        if (tid == 0) {
+            const uint32_t bytes = (uint32_t)((size_t)rows * d * 4);
+            umma::bulk_store_1d(xhi + (dst_row0 + r0) * d, th, bytes);
+            umma::bulk_store_1d(xlo + (dst_row0 + r0) * d, tl, bytes);
+            umma::bulk_commit();
+            const long long tn = t + (long long)STMA_STAGES * stride;
+            if (tn < t_end) {
+                umma::bulk_wait_read<0>();         // this stage's buffers have been read by the stores just issued
+                issue(tn, st);
+            }
+        }
+        // the next iteration uses the OTHER stage; this stage is touched again only after thread 0 re-armed it and
+        // its mbarrier completed, so no further barrier is needed here
+    }
+    if (tid == 0) umma::bulk_wait<0>();            // the planes are in global memory before the kernel ends
+}
+
 // ---------------------------------------------------------------------------
 // K5: per-instance bookkeeping of one chunk (times t_a .. t_a + n - 1).
 // ---------------------------------------------------------------------------
@@ -295,6 +381,12 @@ struct BEngine {
 };
 
 extern "C" void mused_count_launches(uint64_t n);
+
+static bool stage_simt() {            // MUSED_STAGE_SIMT=1: the SIMT append kernels also for TMA-eligible calls (diagnostic)
+    static int v = -1;
+    if (v < 0) v = getenv("MUSED_STAGE_SIMT") ? 1 : 0;
+    return v == 1;
+}
 
 static size_t b_dtype_size(int dt) {
     switch (dt) {
@@ -672,7 +764,17 @@ static int stage_rows(BEngine& E, const void* dev_rows, long long m, long long l
     switch (dtype) {
         case MUSED_F64: STAGE_(double); break;
         case MUSED_F32:
-            if (D.d_l % 4 == 0 && ld % 4 == 0 && stream_stride % 4 == 0 && ((uintptr_t)dev_rows & 15) == 0)
+            if (ld == D.d && D.d_l == D.d && D.d * 4 <= STMA_TILE_BYTES && stream_stride % 4 == 0 &&
+                ((uintptr_t)dev_rows & 15) == 0 && m >= 64 && !stage_simt()) {
+                // TMA-staged append (contiguous fp32 rows): persistent CTAs, whole-row tiles of <= 16 KB
+                const int RT = (int)(STMA_TILE_BYTES / (D.d * 4));
+                const size_t smem = 2 * STMA_STAGES * STMA_TILE_BYTES + 64;
+                MUSED_SMEM_ATTR(k_bstage_tma, smem);
+                const long long tiles = (m + RT - 1) / RT;
+                const unsigned gx = (unsigned)std::min<long long>(tiles, std::max(1, 3 * E.sm_count / E.K));
+                k_bstage_tma<<<dim3(gx, (unsigned)E.K), STMA_NT, smem, st>>>((const float*)dev_rows, stream_stride, D.xrows, D.d, m, RT,
+                                                                         row_off, D.xhi, D.xlo, D.norm2);
+            } else if (D.d_l % 4 == 0 && ld % 4 == 0 && stream_stride % 4 == 0 && ((uintptr_t)dev_rows & 15) == 0)
                 k_bstage_v4<<<dim3((unsigned)std::min<long long>((m + 7) / 8, std::max(1ll, 16ll * E.sm_count / E.K)), (unsigned)E.K), 256, 0, st>>>(
                     (const float*)dev_rows, ld, stream_stride, D.xrows, D.d_l, D.d, m, row_off, D.xhi, D.xlo, D.norm2);
             else
