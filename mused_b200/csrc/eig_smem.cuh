@@ -490,6 +490,13 @@ __global__ void __launch_bounds__(ES_NT, (EPL <= 8 ? 2 : 1)) k_eig_jacobi(EigArg
         if (rank == 0 && tid == 0) sl.skip = 1;
         return;
     }
+#ifdef MUSED_EIG_PROF
+    long long kp[6];
+    kp[0] = clock64();
+#define ES_KSTAMP(i) kp[i] = clock64()
+#else
+#define ES_KSTAMP(i)
+#endif
     const int q_head = sl.q_head, q_len = sl.q_len;
     const unsigned long long last_dump = sl.last_dump;
     const double thr = sl.error;
@@ -535,7 +542,9 @@ __global__ void __launch_bounds__(ES_NT, (EPL <= 8 ? 2 : 1)) k_eig_jacobi(EigArg
                 Wf[c * N2 + lane + 32 * e] = (float)(Gs[(size_t)(rank * ES_CPC + c) * N2 + lane + 32 * e] * inv);
         }
         __syncthreads();
+        ES_KSTAMP(1);
         sweeps32 = es_sweeps<float, EPL, true>(smem, cur, A.tol32, A.max_sweeps, NC, rank, par, off);
+        ES_KSTAMP(2);
         // ---- is every column's direction trustworthy?  (see the note on rank-deficient Grams in DESIGN.md 5) --
         float* Wc = Wf + cur * ES_CPC * N2;
         double tmax = 0.0, tmin = DBL_MAX;
@@ -595,6 +604,7 @@ __global__ void __launch_bounds__(ES_NT, (EPL <= 8 ? 2 : 1)) k_eig_jacobi(EigArg
     // After a mixed-precision solve the result is CHECKED: sum of lambda^2 must equal ||G||_F^2 (1e-6 relative; a
     // restart basis V32 that was not orthonormal fails it by orders of magnitude); a failed check repeats the
     // float64 sweeps from G itself.
+    ES_KSTAMP(3);
     int sweeps_done = 0;
     double lamv[CW];
 #pragma unroll 1
@@ -633,6 +643,7 @@ __global__ void __launch_bounds__(ES_NT, (EPL <= 8 ? 2 : 1)) k_eig_jacobi(EigArg
         cluster_barrier();                      // everyone has read lam
     }
     sweeps_done += 100 * sweeps32;
+    ES_KSTAMP(4);
 
     // rank (descending, ties by column position) of my columns
     int rk[CW];
@@ -714,6 +725,12 @@ __global__ void __launch_bounds__(ES_NT, (EPL <= 8 ? 2 : 1)) k_eig_jacobi(EigArg
         }
     }
     cluster_barrier();                          // no CTA leaves while its shared memory may still be written
+#ifdef MUSED_EIG_PROF
+    ES_KSTAMP(5);
+    if (blockIdx.x == 17 && w == 3 && lane == 0)
+        printf("K3 prof kernel: prologue %lld, float32 sweeps %lld, W = G V32 %lld, float64 sweeps + check %lld, epilogue %lld cycles\n",
+               kp[1] - kp[0], kp[2] - kp[1], kp[3] - kp[2], kp[4] - kp[3], kp[5] - kp[4]);
+#endif
 }
 
 }  // namespace mused
