@@ -108,6 +108,24 @@ def test_cosine_assign_screening_path_gives_the_exact_labels(kind, n, d, k, tau)
         assert frac < 0.02
 
 
+@pytest.mark.parametrize("n,d,k", [(1, 32, 1), (129, 32, 5), (777, 96, 17), (5000, 64, 256), (148 * 256 + 5, 128, 33),
+                                   (2 * 148 * 256 + 131, 32, 150), (4097, 2048, 96)])
+def test_cosine_assign_screening_shapes(n, d, k):
+    """Shapes around the screening kernel's tiling: one K block, fewer K blocks than pipeline stages, one centroid,
+    the widest accumulator (k = 256), both tile heights with ragged tails, several tiles per persistent CTA."""
+    from mused_b200 import matrix_operations as mo
+    rng = np.random.default_rng(n + d + k)
+    C = rng.standard_normal((k, d)).astype(np.float32)
+    X = (C[rng.integers(0, k, n)] + 0.7 * rng.standard_normal((n, d))).astype(np.float32)
+    X[::5] = rng.standard_normal((len(X[::5]), d))
+    tau = 0.35
+    ref, best, gap = ops_oracle.cosine_assign(X, C, tau)
+    lab = mo.cosine_assign(X, C, tau).cpu().numpy()
+    assert lab.min() >= -1 and lab.max() < k
+    sure = (gap > TIE) & (np.abs(best - tau) > TIE) if k > 1 else (np.abs(best - tau) > TIE)
+    assert np.array_equal(lab[sure], ref[sure])
+
+
 def test_screening_operand_semantics_of_the_tensor_core():
     """assign_tc.cuh's error bound assumes that kind::tf32 UMMAs use the upper 19 bits of the fp32 words TMA
     delivered (truncation, relative error < 2^-10) -- measured here.  Rows x = (1 + 2^-11 + 2^-13) * c with c = ones
